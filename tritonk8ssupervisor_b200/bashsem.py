@@ -1,0 +1,435 @@
+"""The handful of bash behaviours the reference's results depend on, restated.
+
+The reference is a bash script, and a surprising amount of what it writes to
+disk is decided not by its own logic but by what bash does to a string on the
+way through: ``read`` without ``-r`` eats backslashes (setup.sh:99,101,472),
+every ``echo $VAR`` is unquoted and so field-splits and pathname-expands its
+value (setup.sh:104-106,130-131,265 and ~30 more sites), ``echo`` itself takes a
+leading ``-n``/``-e`` in the *data* as an option, ``[[ a == $b ]]`` treats an
+unquoted right-hand side as a pattern (setup.sh:345,388,442) and ``$(...)``
+drops trailing newlines.  A replacement that wants byte-identical files has to
+do the same things to the same strings, so they are written down here once, as
+plain functions on ``str``, and checked against the real ``bash`` in
+tests/test_bashsem.py.
+
+Locale: everything here is the C locale (``LC_ALL=C``): bytes compare and sort
+by value, ``[a-z]`` is ASCII.  Strings are ``str`` decoded with
+``surrogateescape`` so arbitrary bytes survive a round trip.
+"""
+from __future__ import annotations
+
+import os
+import re
+from typing import Callable, Iterable, List, Optional, Sequence, Tuple
+
+IFS_WS = " \t\n"
+
+
+def to_bytes(s: str) -> bytes:
+    return s.encode("utf-8", "surrogateescape")
+
+
+def from_bytes(b: bytes) -> str:
+    return b.decode("utf-8", "surrogateescape")
+
+
+def c_sort_key(s: str) -> bytes:
+    """Collation of ``sort``/``ls``/glob results under LC_ALL=C."""
+    return to_bytes(s)
+
+
+# ---------------------------------------------------------------------------
+# read  (bash builtin, no -r, one variable, default IFS)
+# ---------------------------------------------------------------------------
+def read_builtin(next_byte: Callable[[], Optional[int]]) -> Tuple[str, bool]:
+    """``read var``: returns (value, ok); ok is False when EOF came before a
+    newline (bash's ``read`` then returns non-zero but still assigns).
+
+    ``next_byte`` returns the next byte of stdin or None at EOF; it is called
+    once per byte so that nothing beyond the newline is consumed -- children
+    that inherit stdin see the rest, as they do under bash.
+    """
+    chars: List[Tuple[int, bool]] = []  # (byte, escaped)
+    ok = True
+    pending_backslash = False
+    while True:
+        b = next_byte()
+        if b is None:
+            ok = False
+            break
+        if pending_backslash:
+            pending_backslash = False
+            if b == 0x0A:
+                continue  # backslash-newline: line continuation
+            if b != 0:
+                chars.append((b, True))
+            continue
+        if b == 0x5C:
+            pending_backslash = True
+            continue
+        if b == 0x0A:
+            break
+        if b == 0:
+            continue  # read drops NUL bytes
+        chars.append((b, False))
+    # One variable: leading unescaped IFS whitespace goes.  If what is left is a
+    # single field, that field is the value (escaped blanks are part of it).  If
+    # there are more fields, bash assigns the whole remainder and then strips
+    # trailing blanks *whether escaped or not* (strip_trailing_ifs_whitespace).
+    ws = (0x20, 0x09, 0x0A)
+    start, end = 0, len(chars)
+    while start < end and chars[start][0] in ws and not chars[start][1]:
+        start += 1
+    k = start
+    while k < end and not (chars[k][0] in ws and not chars[k][1]):
+        k += 1
+    first_end = k
+    while k < end and chars[k][0] in ws and not chars[k][1]:
+        k += 1
+    if k >= end:
+        end = first_end
+    else:
+        while end > start and chars[end - 1][0] in ws:
+            end -= 1
+    if pending_backslash and start == end:
+        # bash quirk: a lone backslash cut off by EOF leaves its internal
+        # quoting byte (CTLESC, 0x01) in the variable
+        return "\x01", ok
+    return from_bytes(bytes(c for c, _ in chars[start:end])), ok
+
+
+# ---------------------------------------------------------------------------
+# field splitting and pathname expansion of an unquoted expansion
+# ---------------------------------------------------------------------------
+def split_fields(s: str) -> List[str]:
+    """Field splitting of an unquoted ``$var`` with the default IFS."""
+    return [w for w in re.split(r"[ \t\n]+", s) if w]
+
+
+def _has_glob_chars(word: str) -> bool:
+    """bash's unquoted_glob_pattern_p: does this word need pathname expansion?"""
+    open_br = False
+    i, n = 0, len(word)
+    while i < n:
+        c = word[i]
+        i += 1
+        if c in "?*":
+            return True
+        if c == "[":
+            open_br = True
+        elif c == "]":
+            if open_br:
+                return True
+        elif c == "/":
+            open_br = False
+        elif c == "\\":
+            if i < n and word[i] != "/":
+                i += 1
+            elif i >= n:
+                return False
+    return False
+
+
+_CLASSES = {
+    "alpha": "a-zA-Z", "digit": "0-9", "alnum": "0-9a-zA-Z", "upper": "A-Z", "lower": "a-z",
+    "space": " \\t\\n\\r\\f\\v", "blank": " \\t", "punct": re.escape("!\"#$%&'()*+,-./:;<=>?@[\\]^_`{|}~"),
+    "print": "\\x20-\\x7e", "graph": "\\x21-\\x7e", "cntrl": "\\x00-\\x1f\\x7f", "xdigit": "0-9A-Fa-f",
+    "word": "0-9a-zA-Z_",
+}
+
+
+def _bracket_to_regex(pat: str, i: int) -> Tuple[Optional[str], int]:
+    """Translate the bracket expression starting after '[' at pat[i:].
+    Returns (regex, index after ']') or (None, i) when there is no closing ']'
+    (the '[' is then an ordinary character)."""
+    n = len(pat)
+    j = i
+    negate = False
+    if j < n and pat[j] in "!^":
+        negate = True
+        j += 1
+    items: List[str] = []
+    first = True
+    while True:
+        if j >= n:
+            return None, i
+        c = pat[j]
+        if c == "]" and not first:
+            j += 1
+            break
+        first = False
+        if c == "[" and j + 1 < n and pat[j + 1] in ":.=":
+            kind = pat[j + 1]
+            close = pat.find(kind + "]", j + 2)
+            if close != -1:
+                name = pat[j + 2:close]
+                if kind == ":":
+                    if name not in _CLASSES:
+                        return None, i
+                    items.append(_CLASSES[name])
+                else:
+                    items.append(re.escape(name))
+                j = close + 2
+                continue
+        if c == "\\" and j + 1 < n:
+            j += 1
+            c = pat[j]
+        if c == "/":
+            # a slash cannot be matched by a bracket expression in a pathname
+            return None, i
+        lo = c
+        j += 1
+        if j + 1 < n and pat[j] == "-" and pat[j + 1] != "]":
+            hi = pat[j + 1]
+            j += 2
+            if hi == "\\" and j < n:
+                hi = pat[j]
+                j += 1
+            if ord(lo) > ord(hi):
+                # invalid range: matches nothing (bash returns no match)
+                items.append("")
+                continue
+            items.append("%s-%s" % (re.escape(lo), re.escape(hi)))
+        else:
+            items.append(re.escape(lo))
+    body = "".join(items)
+    if not body:
+        return ("[\\s\\S]" if negate else "(?!)"), j
+    return "[%s%s]" % ("^" if negate else "", body), j
+
+
+def glob_to_regex(pat: str, pathname: bool = True) -> str:
+    """Shell pattern -> anchored Python regex (C locale)."""
+    out: List[str] = []
+    i, n = 0, len(pat)
+    nonslash = "[^/]" if pathname else "[\\s\\S]"
+    while i < n:
+        c = pat[i]
+        i += 1
+        if c == "*":
+            out.append(nonslash + "*")
+        elif c == "?":
+            out.append(nonslash)
+        elif c == "[":
+            rx, j = _bracket_to_regex(pat, i)
+            if rx is None:
+                out.append(re.escape("["))
+            else:
+                out.append(rx)
+                i = j
+        elif c == "\\":
+            if i < n:
+                out.append(re.escape(pat[i]))
+                i += 1
+            else:
+                out.append(re.escape("\\"))
+        else:
+            out.append(re.escape(c))
+    return "(?s:" + "".join(out) + r")\Z"
+
+
+def pattern_match(s: str, pat: str) -> bool:
+    """``[[ $s == $pat ]]`` with an unquoted right-hand side (setup.sh:345,388,442)."""
+    return re.match(glob_to_regex(pat, pathname=False), s) is not None
+
+
+def _glob_component(pattern: str) -> Callable[[str], bool]:
+    rx = re.compile(glob_to_regex(pattern, pathname=True))
+    leading_dot_ok = pattern.startswith(".") or pattern.startswith("\\.")
+
+    def match(name: str) -> bool:
+        if name in (".", ".."):
+            return False  # globskipdots (default on in bash 5.2)
+        if name.startswith(".") and not leading_dot_ok:
+            return False
+        return rx.match(name) is not None
+    return match
+
+
+def _unescape_glob(s: str) -> str:
+    return re.sub(r"\\(.)", r"\1", s, flags=re.S)
+
+
+def glob_word(word: str, cwd: str) -> List[str]:
+    """Pathname expansion of one field; the word itself when nothing matches."""
+    if not _has_glob_chars(word):
+        return [word]
+    absolute = word.startswith("/")
+    parts = word.split("/")
+    # candidates are (display path, filesystem path)
+    cands: List[Tuple[str, str]] = [("/" if absolute else "", "/" if absolute else cwd)]
+    comps = parts[1:] if absolute else parts
+    for idx, comp in enumerate(comps):
+        last = idx == len(comps) - 1
+        nxt: List[Tuple[str, str]] = []
+        if comp == "":
+            # "a//b" or trailing slash: keep the slash, require a directory
+            for disp, fs in cands:
+                if last:
+                    if os.path.isdir(fs):
+                        nxt.append((disp + "/" if not disp.endswith("/") else disp, fs))
+                else:
+                    nxt.append((disp + "/" if disp and not disp.endswith("/") else disp, fs))
+            cands = nxt
+            continue
+        if _has_glob_chars(comp):
+            m = _glob_component(comp)
+            for disp, fs in cands:
+                try:
+                    names = os.listdir(fs)
+                except OSError:
+                    continue
+                for name in sorted(names, key=c_sort_key):
+                    if m(name):
+                        p = os.path.join(fs, name)
+                        if last or os.path.isdir(p):
+                            nxt.append((_join_disp(disp, name), p))
+        else:
+            name = _unescape_glob(comp)
+            for disp, fs in cands:
+                p = os.path.join(fs, name)
+                if os.path.lexists(p) and (last or os.path.isdir(p)):
+                    nxt.append((_join_disp(disp, name), p))
+        cands = nxt
+        if not cands:
+            break
+    if not cands:
+        return [word]
+    return sorted((d for d, _ in cands), key=c_sort_key)
+
+
+def _join_disp(disp: str, name: str) -> str:
+    if disp == "" or disp.endswith("/"):
+        return disp + name
+    return disp + "/" + name
+
+
+def expand_unquoted(s: str, cwd: str) -> List[str]:
+    """What an unquoted ``$var`` becomes: fields, each pathname-expanded."""
+    out: List[str] = []
+    for w in split_fields(s):
+        out.extend(glob_word(w, cwd))
+    return out
+
+
+def expand_word(segments: Sequence[Tuple[str, bool]], cwd: str) -> List[str]:
+    """Expand one shell word made of literal text and unquoted substitutions.
+
+    ``segments`` is a list of (text, is_unquoted_expansion).  Literal text
+    glues to the neighbouring fields the way it does in the shell:
+    ``http://$(cat f):8080`` with a two-line ``f`` gives two words
+    (setup.sh:66)."""
+    words: List[str] = []
+    cur: Optional[str] = None
+    for text, is_exp in segments:
+        if not is_exp:
+            cur = (cur or "") + text
+            continue
+        if text == "":
+            continue
+        fields = split_fields(text)
+        if not fields:
+            # only IFS whitespace: it still terminates the current field
+            if cur is not None:
+                words.append(cur)
+                cur = None
+            continue
+        if text[0] in IFS_WS and cur is not None:
+            words.append(cur)
+            cur = None
+        for k, f in enumerate(fields):
+            if k == 0:
+                cur = (cur or "") + f
+            else:
+                words.append(cur)  # type: ignore[arg-type]
+                cur = f
+        if text[-1] in IFS_WS:
+            words.append(cur)  # type: ignore[arg-type]
+            cur = None
+    if cur is not None:
+        words.append(cur)
+    out: List[str] = []
+    for w in words:
+        out.extend(glob_word(w, cwd))
+    return out
+
+
+# ---------------------------------------------------------------------------
+# echo  (bash builtin, xpg_echo off)
+# ---------------------------------------------------------------------------
+_ECHO_OPT = re.compile(r"-[neE]+\Z")
+
+
+def _echo_escapes(s: str) -> Tuple[str, bool]:
+    """Backslash processing of ``echo -e``; returns (text, stop) where stop is
+    True after ``\\c``."""
+    out: List[str] = []
+    i, n = 0, len(s)
+    simple = {"a": "\a", "b": "\b", "e": "\x1b", "E": "\x1b", "f": "\f", "n": "\n",
+              "r": "\r", "t": "\t", "v": "\v", "\\": "\\"}
+    while i < n:
+        c = s[i]
+        i += 1
+        if c != "\\" or i >= n:
+            out.append(c)
+            continue
+        d = s[i]
+        i += 1
+        if d in simple:
+            out.append(simple[d])
+        elif d == "c":
+            return "".join(out), True
+        elif d == "0":
+            # echo -e takes octal only in the \0nnn form (up to three digits)
+            digits = 3
+            val = 0
+            while digits and i < n and s[i] in "01234567":
+                val = val * 8 + int(s[i])
+                i += 1
+                digits -= 1
+            out.append(from_bytes(bytes([val & 0xFF])))
+        elif d == "x":
+            j = i
+            while j < n and j - i < 2 and s[j] in "0123456789abcdefABCDEF":
+                j += 1
+            if j == i:
+                out.append("\\x")
+            else:
+                out.append(from_bytes(bytes([int(s[i:j], 16) & 0xFF])))
+                i = j
+        else:
+            out.append("\\" + d)
+    return "".join(out), False
+
+
+def echo_builtin(args: Sequence[str]) -> str:
+    """Exactly what ``echo ARGS...`` writes (including the trailing newline,
+    or not)."""
+    newline, escapes = True, False
+    k = 0
+    while k < len(args) and _ECHO_OPT.match(args[k]):
+        for ch in args[k][1:]:
+            if ch == "n":
+                newline = False
+            elif ch == "e":
+                escapes = True
+            else:
+                escapes = False
+        k += 1
+    text = " ".join(args[k:])
+    if escapes:
+        text, stop = _echo_escapes(text)
+        if stop:
+            return text
+    return text + ("\n" if newline else "")
+
+
+def cmdsubst(output: str) -> str:
+    """``$(...)``: trailing newlines dropped, NUL bytes dropped."""
+    return output.replace("\x00", "").rstrip("\n")
+
+
+def echo_unquoted(value: str, cwd: str) -> str:
+    """``echo $value`` -- the workhorse of the reference (unquoted on purpose
+    there or not, it is what decides the bytes)."""
+    return echo_builtin(expand_unquoted(value, cwd))

@@ -1,0 +1,151 @@
+#!/bin/sh
+# Offline stand-in for every external tool the provisioning path shells out to
+# (triton, ssh-keygen, terraform, ansible-playbook, curl, ssh, date, sleep).
+#
+# One script, installed under each tool's name in a scratch bin/ directory that
+# is put first on PATH; it dispatches on basename($0).  Behaviour is scripted by
+# plain files under $TK8S_STUB_STATE, and every invocation is appended to
+# $TK8S_STUB_STATE/calls.log as "<tool>|<cwd relative to the workspace>|<argv>".
+#
+# The contracts mirrored here are the ones the reference relies on:
+#   triton env|networks|packages      setup.sh:210,257,259,536,541
+#   ssh-keygen -E md5 -lf / -l -f / -R setup.sh:217-224,506
+#   terraform get|apply|destroy -force setup.sh:156-157,501 and the local-exec
+#       IP capture of terraform/{master,host}/main.tf:29-31
+#   ansible-playbook -i hosts clusterUp.yml   setup.sh:113
+#   curl / ssh / date / sleep in the dashboard wait loop   setup.sh:59-85
+tool=$(basename "$0")
+S=${TK8S_STUB_STATE:?TK8S_STUB_STATE not set}
+root=${TK8S_STUB_ROOT:-$PWD}
+case "$PWD" in
+    "$root") rel=. ;;
+    "$root"/*) rel=./${PWD#"$root"/} ;;
+    *) rel=$PWD ;;
+esac
+printf '%s|%s|%s\n' "$tool" "$rel" "$*" >> "$S/calls.log"
+# the provisioning tools also see the exported configuration (setup.sh:543-549):
+# record it, literal double quotes and all
+case "$tool" in
+    terraform|ansible-playbook)
+        env | grep -E '^(SDC_|KUBERNETES_|RANCHER_|HOST_PACKAGE=|ANSIBLE_|TRITON_)' | LC_ALL=C sort | sed 's/^/  env:/' >> "$S/calls.log"
+        ;;
+esac
+
+# scripted failure: a file fail/<tool>-<first arg> holding the exit status
+sub=${1:-}
+if [ -f "$S/fail/$tool-$sub" ]; then
+    msg="$S/fail/$tool-$sub.stderr"
+    [ -f "$msg" ] && cat "$msg" >&2
+    exit "$(cat "$S/fail/$tool-$sub")"
+fi
+
+# next value of a per-tool sequence: prints file <dir>/<n> (n = 1,2,...) or <dir>/default
+seq_next() {
+    n=0
+    [ -f "$S/$1.n" ] && n=$(cat "$S/$1.n")
+    n=$((n + 1))
+    echo "$n" > "$S/$1.n"
+    if [ -f "$S/$1/$n" ]; then
+        cat "$S/$1/$n"
+    elif [ -f "$S/$1/default" ]; then
+        cat "$S/$1/default"
+    else
+        return 1
+    fi
+}
+
+case "$tool" in
+triton)
+    case "$sub" in
+        env) cat "$S/triton_env.txt" ;;
+        networks) cat "$S/networks.txt" ;;
+        packages) cat "$S/packages.txt" ;;
+        *) echo "triton stub: unsupported: $*" >&2; exit 2 ;;
+    esac
+    ;;
+ssh-keygen)
+    case "$sub" in
+        -E)
+            # modern form: ssh-keygen -E md5 -lf <path>
+            [ -f "$S/keygen_no_E" ] && { echo "ssh-keygen: illegal option -- E" >&2; exit 1; }
+            path=$4
+            [ -f "$path" ] || { echo "ssh-keygen: $path: No such file or directory" >&2; exit 255; }
+            f="$S/keygen/$(basename "$path")"
+            [ -f "$f" ] || { echo "$path is not a public key file." >&2; exit 255; }
+            cat "$f"
+            ;;
+        -l)
+            # legacy form: ssh-keygen -l -f <path>
+            path=$3
+            [ -f "$path" ] || { echo "ssh-keygen: $path: No such file or directory" >&2; exit 255; }
+            f="$S/keygen_legacy/$(basename "$path")"
+            [ -f "$f" ] || f="$S/keygen_sha/$(basename "$path")"
+            [ -f "$f" ] || { echo "$path is not a public key file." >&2; exit 255; }
+            cat "$f"
+            ;;
+        -R)
+            echo "# Host $2 found: line 1"
+            echo "$HOME/.ssh/known_hosts updated." >&2
+            ;;
+        *) echo "ssh-keygen stub: unsupported: $*" >&2; exit 2 ;;
+    esac
+    ;;
+terraform)
+    case "$sub" in
+        get)
+            echo "Get: file://$rel/master"
+            ;;
+        apply)
+            [ -f "$S/terraform_no_ips" ] && { echo "Error applying plan: provisioning limit"; exit 0; }
+            master_ip=10.0.0.1
+            [ -f "$S/master_ip" ] && master_ip=$(cat "$S/master_ip")
+            i=0
+            # one IP per module block, in file order, the way local-exec appends them
+            grep 'source = ' rancher.tf | while read -r _ _ src; do
+                case "$src" in
+                    '"master"') echo "$master_ip" >> masters.ip ;;
+                    '"host"') i=$((i + 1)); echo "10.0.1.$i" >> hosts.ip ;;
+                esac
+            done
+            echo "Apply complete! Resources: $(grep -c 'source = ' rancher.tf) added, 0 changed, 0 destroyed."
+            ;;
+        destroy)
+            echo "Destroy complete!"
+            ;;
+        *) echo "terraform stub: unsupported: $*" >&2; exit 2 ;;
+    esac
+    ;;
+ansible-playbook)
+    echo "PLAY RECAP (stub) $*"
+    if [ -f "$S/env_id" ]; then
+        mkdir -p tmp
+        cat "$S/env_id" > tmp/kubernetes_environment.id
+    fi
+    ;;
+curl)
+    seq_next curl || echo "<title>Kubernetes Dashboard</title>"
+    ;;
+ssh)
+    # ssh -o StrictHostKeyChecking=no root@<ip> docker ps | "docker stop -t0 <id>"
+    target=$3
+    ip=${target#root@}
+    case "$4" in
+        docker)
+            [ -f "$S/ssh/$ip.ps" ] && cat "$S/ssh/$ip.ps"
+            ;;
+        *) : ;;
+    esac
+    if [ -f "$S/ssh/$ip.exit" ]; then exit "$(cat "$S/ssh/$ip.exit")"; fi
+    ;;
+date)
+    seq_next date || echo 1500000000
+    ;;
+sleep)
+    :
+    ;;
+*)
+    echo "stubtool: no behaviour for $tool" >&2
+    exit 127
+    ;;
+esac
+exit 0

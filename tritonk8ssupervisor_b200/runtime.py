@@ -1,0 +1,172 @@
+"""The process boundary of the path: stdin/stdout/stderr, child processes, the
+clock and the workspace directory.
+
+The reference script touches the outside world in exactly these ways, and the
+replacement does so only through a :class:`Runtime`, so the same path logic runs
+
+* as a command-line program on a real machine (:class:`HostRuntime`, file
+  descriptors 0/1/2, tools found on ``PATH``), and
+* in-process against in-memory tool models for property tests and for the
+  resident-input leg of ``bench.py`` (:class:`tritonk8ssupervisor_b200.conformance.modeltools.ModelRuntime`).
+
+Child processes inherit stdin/stdout/stderr exactly where the reference lets them
+(terraform and ansible output interleaves with the script's own lines), and stdin
+is consumed one byte at a time so a child that reads stdin sees what it would see
+under bash.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+import time
+from typing import Dict, List, Optional, Sequence, Tuple
+
+from . import bashsem
+
+INHERIT, DEVNULL, CAPTURE, TO_STDOUT = "inherit", "devnull", "capture", "to_stdout"
+
+
+class ScriptExit(Exception):
+    """The script ends with this status (bash ``exit N`` or errexit)."""
+
+    def __init__(self, status: int):
+        super().__init__(status)
+        self.status = status
+
+
+class Runtime:
+    """Abstract boundary; see :class:`HostRuntime`."""
+
+    root: str
+    env: Dict[str, str]
+
+    # -- terminal ----------------------------------------------------------
+    def out(self, text: str) -> None:
+        raise NotImplementedError
+
+    def err(self, text: str) -> None:
+        raise NotImplementedError
+
+    def read(self, prompt: str) -> Tuple[str, bool]:
+        """bash ``read -p PROMPT var``."""
+        raise NotImplementedError
+
+    # -- children ----------------------------------------------------------
+    def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
+            stderr: str = INHERIT) -> Tuple[int, str]:
+        """Run a tool; returns (exit status, captured stdout or '')."""
+        raise NotImplementedError
+
+    def sleep(self, seconds: int) -> int:
+        raise NotImplementedError
+
+    def epoch(self) -> str:
+        """Output of ``date +%s`` (with its newline)."""
+        raise NotImplementedError
+
+    # -- filesystem (all paths relative to the workspace root) --------------
+    def path(self, rel: str) -> str:
+        return os.path.join(self.root, rel)
+
+    def exists(self, rel: str) -> bool:
+        return os.path.exists(self.path(rel))
+
+    def read_text(self, rel: str) -> str:
+        with open(self.path(rel), "rb") as fh:
+            return bashsem.from_bytes(fh.read())
+
+    def write_text(self, rel: str, text: str) -> None:
+        with open(self.path(rel), "wb") as fh:
+            fh.write(bashsem.to_bytes(text))
+
+    def append_text(self, rel: str, text: str) -> None:
+        with open(self.path(rel), "ab") as fh:
+            fh.write(bashsem.to_bytes(text))
+
+    def home(self) -> str:
+        return self.env.get("HOME", "")
+
+
+class HostRuntime(Runtime):
+    """The real thing: fds 0/1/2, ``subprocess``, wall clock.
+
+    ``external_clock`` makes ``sleep`` and ``date +%s`` child processes found on
+    ``PATH`` (what the reference does, setup.sh:36,62,64) instead of in-process
+    calls, so a scripted ``date``/``sleep`` on ``PATH`` controls time in offline
+    runs.  It is switched on with ``TK8S_EXTERNAL_CLOCK=1``.
+    """
+
+    def __init__(self, root: str = ".", env: Optional[Dict[str, str]] = None,
+                 stdin_fd: int = 0, stdout_fd: int = 1, stderr_fd: int = 2,
+                 external_clock: Optional[bool] = None):
+        self.root = root
+        self.env = dict(os.environ if env is None else env)
+        self.stdin_fd, self.stdout_fd, self.stderr_fd = stdin_fd, stdout_fd, stderr_fd
+        if external_clock is None:
+            external_clock = self.env.get("TK8S_EXTERNAL_CLOCK", "") == "1"
+        self.external_clock = external_clock
+        try:
+            self._tty = os.isatty(stdin_fd)
+        except OSError:
+            self._tty = False
+
+    def out(self, text: str) -> None:
+        _write_all(self.stdout_fd, bashsem.to_bytes(text))
+
+    def err(self, text: str) -> None:
+        _write_all(self.stderr_fd, bashsem.to_bytes(text))
+
+    def _next_byte(self) -> Optional[int]:
+        try:
+            b = os.read(self.stdin_fd, 1)
+        except OSError:
+            return None
+        return b[0] if b else None
+
+    def read(self, prompt: str) -> Tuple[str, bool]:
+        if self._tty:
+            # bash prints the -p prompt (on stderr) only when stdin is a terminal
+            self.err(prompt)
+        return bashsem.read_builtin(self._next_byte)
+
+    def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
+            stderr: str = INHERIT) -> Tuple[int, str]:
+        out_target = {INHERIT: self.stdout_fd, DEVNULL: subprocess.DEVNULL,
+                      CAPTURE: subprocess.PIPE}[stdout]
+        err_target = {INHERIT: self.stderr_fd, DEVNULL: subprocess.DEVNULL,
+                      TO_STDOUT: self.stdout_fd}[stderr]
+        try:
+            proc = subprocess.Popen(list(argv), cwd=self.path(cwd), env=self.env,
+                                    stdin=self.stdin_fd, stdout=out_target, stderr=err_target)
+        except FileNotFoundError:
+            if stderr == INHERIT:
+                self.err("%s: command not found\n" % argv[0])
+            return 127, ""
+        except PermissionError:
+            if stderr == INHERIT:
+                self.err("%s: Permission denied\n" % argv[0])
+            return 126, ""
+        data, _ = proc.communicate()
+        status = proc.returncode
+        if status < 0:
+            status = 128 - status
+        return status, (bashsem.from_bytes(data) if data is not None else "")
+
+    def sleep(self, seconds: int) -> int:
+        if self.external_clock:
+            return self.run(["sleep", str(seconds)])[0]
+        time.sleep(seconds)
+        return 0
+
+    def epoch(self) -> str:
+        if self.external_clock:
+            return self.run(["date", "+%s"], stdout=CAPTURE)[1]
+        return "%d\n" % int(time.time())
+
+
+def _write_all(fd: int, data: bytes) -> None:
+    view = memoryview(data)
+    while view:
+        n = os.write(fd, view)
+        view = view[n:]

@@ -1,0 +1,836 @@
+"""The provisioning path: prompts -> ``./config`` -> ``terraform/rancher.tf`` ->
+(terraform) -> ``ansible/hosts``, ``vars.yml``, ``ansible.cfg`` -> (ansible) ->
+dashboard wait loop; and ``-c`` (clean).
+
+This is a from-scratch replacement for the reference's ``setup.sh`` behind the
+same process/CLI/filesystem boundary: same answers on stdin,
+same child processes with the same argv in the same order and environment, same
+bytes on stdout and in every generated file, same exit statuses -- including
+the ones that look wrong (exit 0 from the previous-run guard, setup.sh:14-18).
+
+Design, as opposed to the reference's: the eight prompts are data
+(:class:`Prompt` records driven by one loop, where the reference has eight
+copy-pasted blocks), the three Terraform block shapes come from one emitter, and
+everything bash does to a string implicitly is an explicit call into
+:mod:`bashsem` / :mod:`textops`.  All I/O goes through a :class:`Runtime`, so the
+same code runs as a CLI and in-process.
+
+Function-by-function correspondence (reference file:line):
+
+  main                      setup.sh:8-92
+  set_var_defaults          setup.sh:240-254   (a1)
+  set_config_from_triton    setup.sh:209-239   (a2)
+  get_argument              setup.sh:94-110    (a3)
+  get_config_from_user      setup.sh:255-451   (a4)
+  network_ids / package_id  setup.sh:532-542   (a5, a6)
+  verify_config             setup.sh:452-483   (a7)
+  set_config_to_file        setup.sh:199-208   (a8)
+  export_vars               setup.sh:543-549   (a9)
+  terraform blocks          setup.sh:162-198   (a10-a12)
+  run_terraform_tasks       setup.sh:138-161   (a13)
+  create_ansible_configs    setup.sh:116-137   (a15)
+  run_ansible               setup.sh:111-115
+  wait_for_dashboard        setup.sh:59-85     (§8f rank 2)
+  clean_runner              setup.sh:484-521   (a17, §8f rank 3)
+"""
+from __future__ import annotations
+
+import glob as _glob
+import os
+import re
+import shutil
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+from . import bashsem as sh
+from . import textops as tx
+from .runtime import CAPTURE, DEVNULL, INHERIT, TO_STDOUT, Runtime, ScriptExit
+from .tritonenv import TritonEnvError, apply_triton_env
+
+RULE = "#" * 80
+DASHES = "---------------"
+HOSTNAME_RE = re.compile(r"[a-zA-Z][0-9a-zA-Z]+")            # setup.sh:276,288 (anchored: fullmatch)
+NODE_COUNT_RE = re.compile(r"[1-9]")                         # setup.sh:301
+INDEX_LIST_RE = r"^[1-9][0-9]?(,[1-9][0-9]?)*$"              # setup.sh:337,380 (BRE there)
+INDEX_RE = r"^[1-9][0-9]*$"                                  # setup.sh:428
+_IDENT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
+
+TRITON_NETWORKS = ["triton", "networks", "-oname,id"]
+TRITON_PACKAGES = ["triton", "packages", "-oname,id"]
+
+
+def _to_int64(text: str) -> int:
+    """bash arithmetic on a decimal literal: wraps modulo 2**64 (signed).
+    Anything else evaluates like an unset variable name, i.e. 0."""
+    if not re.fullmatch(r"[0-9]+", text):
+        return 0
+    v = int(text) & 0xFFFFFFFFFFFFFFFF
+    return v - (1 << 64) if v >= (1 << 63) else v
+
+
+class _ShellVars(dict):
+    """Shell variables; assigning to one that is exported updates the
+    environment children get, as in bash."""
+
+    def __init__(self, env: Dict[str, str]):
+        super().__init__(env)
+        self._env = env
+
+    def __setitem__(self, key: str, value: str) -> None:
+        super().__setitem__(key, value)
+        if key in self._env:
+            self._env[key] = value
+
+
+class Supervisor:
+    """One run of the path against a :class:`Runtime`."""
+
+    def __init__(self, rt: Runtime, program: str = "setup.sh"):
+        self.rt = rt
+        self.program = program
+        #: shell variables (the exported ones are mirrored in ``rt.env``)
+        self.v: Dict[str, str] = _ShellVars(rt.env)
+
+    # ------------------------------------------------------------------
+    # small helpers: the shell idioms the reference repeats
+    # ------------------------------------------------------------------
+    def echo(self, line: str = "") -> None:
+        """``echo "<line>"`` with a double-quoted argument."""
+        self.rt.out(sh.echo_builtin([line]))
+
+    def echo_var(self, value: str) -> str:
+        """``$(echo $VALUE)``: unquoted, so field-split and globbed in the workspace."""
+        return sh.cmdsubst(sh.echo_unquoted(value, self.rt.root))
+
+    def unq(self, value: str) -> str:
+        """``$(echo $VALUE | sed 's/"//g')`` -- the reference's quote-stripper."""
+        return sh.cmdsubst(tx.strip_dquotes(sh.echo_unquoted(value, self.rt.root)))
+
+    def args_of(self, value: str) -> List[str]:
+        """Positional parameters produced by an unquoted ``$VALUE`` argument."""
+        return sh.expand_unquoted(value, self.rt.root)
+
+    def append_line(self, rel: str, line: str) -> None:
+        """``echo "<line>" >> rel``; a failing redirection ends the script (errexit)."""
+        try:
+            self.rt.append_text(rel, sh.echo_builtin([line]))
+        except OSError as exc:
+            self._redirect_failed(rel, exc)
+
+    def _redirect_failed(self, rel: str, exc: OSError) -> None:
+        self.rt.err("%s: %s: %s\n" % (self.program, rel, exc.strerror))
+        raise ScriptExit(1)
+
+    def cat_subst(self, rel: str) -> str:
+        """``$(cat rel)``; a missing file costs a message on stderr, not the run."""
+        try:
+            return sh.cmdsubst(self.rt.read_text(rel))
+        except OSError as exc:
+            self.rt.err("cat: %s: %s\n" % (rel, exc.strerror))
+            return ""
+
+    def must(self, status: int) -> None:
+        """errexit: an unguarded child failure is the script's exit status."""
+        if status != 0:
+            raise ScriptExit(status)
+
+    def tilde(self, path: str) -> str:
+        """Tilde expansion of a word starting with ``~/``."""
+        return self.rt.home() + path[1:] if path.startswith("~/") or path == "~" else path
+
+    # ------------------------------------------------------------------
+    # main  (setup.sh:8-92)
+    # ------------------------------------------------------------------
+    def main(self, argv: Sequence[str]) -> int:
+        try:
+            self._main(argv)
+        except ScriptExit as e:
+            return e.status
+        return 0
+
+    def _main(self, argv: Sequence[str]) -> None:
+        rt = self.rt
+        if argv and argv[0] == "-c":
+            self.clean_runner()
+            raise ScriptExit(0)
+        if rt.exists("terraform/rancher.tf"):
+            self.echo("error: configuration for a previous run has been found")
+            self.echo("    clean the configuration (./setup -c)")
+            raise ScriptExit(0)  # bare `exit` after a successful echo
+
+        self.set_var_defaults()
+        self.set_config_from_triton()
+        self.get_config_from_user()
+        self.verify_config()
+        self.set_config_to_file()
+        self.export_vars()
+
+        self.banner("Starting terraform tasks...")
+        self.run_terraform_tasks()
+        self.banner("Creating ansible configs...")
+        self.create_ansible_configs()
+        self.banner("Running ansible tasks...")
+        self.run_ansible()
+
+        master = self.cat_subst("terraform/masters.ip")
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        self.echo("")
+        self.echo("Congratulations, your Kubernetes cluster setup has been complete.")
+        self.echo("")
+        self.echo("It will take a few minutes for all the Kubernetes process to start up before you can access Kubernetes Dashboard")
+        self.echo("----> To check what processes/containers are coming up, go to http://%s:8080/env/%s/infra/containers" % (master, env_id))
+        self.echo("    once all these containers are up, you should be able to access Kubernetes by its dashboard or using CLI")
+        self.echo("Waiting on Kubernetes dashboard to come up.")
+        self.echo("")
+        self.wait_for_dashboard()
+        self.echo("")
+        master = self.cat_subst("terraform/masters.ip")
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        self.echo("----> Kubernetes dashboard is at http://%s:8080/r/projects/%s/kubernetes-dashboard:9090/" % (master, env_id))
+        master = self.cat_subst("terraform/masters.ip")
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        self.echo("----> Kubernetes CLI config is at http://%s:8080/env/%s/kubernetes/kubectl" % (master, env_id))
+        self.echo("")
+        self.echo("    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!")
+
+    def banner(self, text: str) -> None:
+        self.echo(RULE)
+        self.echo("### " + text)
+        self.echo(RULE)
+        self.must(self.rt.sleep(2))
+
+    # ------------------------------------------------------------------
+    # a1  setVarDefaults  (setup.sh:240-254)
+    # ------------------------------------------------------------------
+    def set_var_defaults(self) -> None:
+        if self.rt.exists("config"):
+            self.echo("error: old configuration found")
+            self.clean_runner()
+        v = self.v
+        v["KUBERNETES_NAME"] = "k8s dev"
+        v["KUBERNETES_DESCRIPTION"] = v["KUBERNETES_NAME"]
+        v["RANCHER_MASTER_HOSTNAME"] = "kubemaster"
+        v["KUBERNETES_NODE_HOSTNAME_BEGINSWITH"] = "kubenode"
+        v["KUBERNETES_NUMBER_OF_NODES"] = "1"
+        v["RANCHER_MASTER_NETWORKS"] = ""
+        v["KUBERNETES_NODE_NETWORKS"] = ""
+        v["HOST_PACKAGE"] = ""
+        self.append_line("config", "ANSIBLE_HOST_KEY_CHECKING=False")
+
+    # ------------------------------------------------------------------
+    # a2  setConfigFromTritonENV  (setup.sh:209-239)
+    # ------------------------------------------------------------------
+    def set_config_from_triton(self) -> None:
+        rt, v = self.rt, self.v
+        _, text = rt.run(["triton", "env"], stdout=CAPTURE)  # status is swallowed by eval "$(...)"
+        try:
+            apply_triton_env(sh.cmdsubst(text), v, rt.env)
+        except TritonEnvError as exc:
+            rt.err("%s: %s\n" % (self.program, exc))
+            raise ScriptExit(2)
+        for name in ("SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID"):
+            self.append_line("config", '%s="%s"' % (name, v.get(name, "")))
+
+        key_id = v.get("SDC_KEY_ID", "")
+        found = False
+        for f in self.args_of(self._ls_ssh_dir()):
+            # ~/.ssh/$(echo $f | sed 's/.pub$//') -- unquoted, so it can be several words
+            stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, rt.root), r".pub$", ""))
+            key_args = sh.expand_word([(self.tilde("~/.ssh/"), False), (stem, True)], rt.root)
+            _, out = rt.run(["ssh-keygen", "-E", "md5", "-lf"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
+            fp = sh.cmdsubst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""))
+            if fp == key_id:
+                found = True
+            else:
+                # ssh-keygen too old for -E prints MD5 by default (setup.sh:222-229)
+                _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
+                if sh.cmdsubst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256")) == "":
+                    _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
+                    if sh.cmdsubst(tx.awk_print_field(out, 2)) == key_id:
+                        found = True
+            if found:
+                self.append_line("config", 'SDC_KEY="~/.ssh/%s"' % stem)
+                break
+        if not found:
+            self.echo("error: couldn't find the ssh key associated with fingerprint %s in ~/.ssh/ directory..." % key_id)
+            self.echo("    Clean the setup and make sure your triton profile is set up.")
+            self.echo("    To confirm your profile is set up, try `triton info`.")
+            self.clean_runner()
+            raise ScriptExit(1)
+        self.append_line("config", "")
+
+    def _ls_ssh_dir(self) -> str:
+        """``$(ls ~/.ssh)``: names one per line, C collation, dot files hidden."""
+        d = self.tilde("~/.ssh")
+        try:
+            names = os.listdir(d)
+        except OSError as exc:
+            self.rt.err("ls: cannot access '%s': %s\n" % (d, exc.strerror))
+            return ""
+        names = sorted((n for n in names if not n.startswith(".")), key=sh.c_sort_key)
+        return sh.cmdsubst(tx.unlines(names))
+
+    # ------------------------------------------------------------------
+    # a3  getArgument  (setup.sh:94-110)
+    # ------------------------------------------------------------------
+    def get_argument(self, message: str, default: str) -> str:
+        """``$(getArgument "message" "default")``: empty answer (or EOF) = default.
+        Both branches ``echo`` unquoted."""
+        answer, _ok = self.rt.read("%s (%s) " % (message, default))
+        return self.echo_var(default if answer == "" else answer)
+
+    # ------------------------------------------------------------------
+    # a4  getConfigFromUser  (setup.sh:255-451)
+    # ------------------------------------------------------------------
+    def _menu_rows(self, argv: List[str], kvm_only: bool) -> str:
+        """The table a menu is built from: header dropped, runs of blanks
+        squeezed, blanks turned into '=', sorted (setup.sh:257,259)."""
+        _, text = self.rt.run(argv, stdout=CAPTURE)
+        if kvm_only:
+            text = tx.grep(text, r"-kvm-")
+        text = tx.grep(text, r"^NAME.*ID$", invert=True)
+        return sh.cmdsubst(tx.sort_lines(tx.tr(tx.tr_squeeze_spaces(text), " ", "=")))
+
+    def _print_menu(self, rows: str, default_prefix: Optional[str]) -> Tuple[int, int]:
+        """Numbered menu; returns (row count, 1-based position of the default row)."""
+        count, default_at = 0, 1
+        for row in self.args_of(rows):
+            count += 1
+            shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.rt.root), r"=", "  ", count=0))
+            self.rt.out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]))
+            if default_prefix is not None and row.startswith(default_prefix):
+                default_at = count
+        return count, default_at
+
+    def _prompt_validated(self, message: str, var: str, ok: Callable[[str], bool], errors: List[str]) -> None:
+        default = self.unq(self.v[var])  # evaluated once per attempt in the reference; it cannot change
+        while True:
+            answer = self.get_argument(message, default)
+            if ok(answer):
+                self.v[var] = answer
+                return
+            for line in errors:
+                self.echo(line)
+
+    def get_config_from_user(self) -> None:
+        v = self.v
+        networks = self._menu_rows(TRITON_NETWORKS, kvm_only=False)
+        packages = self._menu_rows(TRITON_PACKAGES, kvm_only=True)
+
+        self.echo(DASHES)
+        v["KUBERNETES_NAME"] = self.get_argument("Name your Kubernetes environment:", self.unq(v["KUBERNETES_NAME"]))
+        self.echo(DASHES)
+        # the description default is whatever the description already holds
+        # ("k8s dev" from the defaults), not the name just entered (setup.sh:267-271)
+        descr_default = v["KUBERNETES_NAME"] if v["KUBERNETES_DESCRIPTION"] == "" else v["KUBERNETES_DESCRIPTION"]
+        v["KUBERNETES_DESCRIPTION"] = self.get_argument("Describe this Kubernetes environment:", self.unq(descr_default))
+        self.echo(DASHES)
+        self._prompt_validated(
+            "Hostname of the master:", "RANCHER_MASTER_HOSTNAME", lambda s: HOSTNAME_RE.fullmatch(s) is not None,
+            ["error: Enter a valid hostname or leave blank to use the default.",
+             "    Must start with a letter and can only include letters and numbers"])
+        self.echo(DASHES)
+        self._prompt_validated(
+            "Enter a string to use for appending to hostnames of all the nodes:", "KUBERNETES_NODE_HOSTNAME_BEGINSWITH",
+            lambda s: HOSTNAME_RE.fullmatch(s) is not None,
+            ["error: Enter a valid value or leave blank to use the default.",
+             "    Must start with a letter and can only include letters and numbers"])
+        self.echo(DASHES)
+        # hard limit 1-9: the setup has no HA (setup.sh:296)
+        self._prompt_validated(
+            "How many nodes should this Kubernetes cluster have:", "KUBERNETES_NUMBER_OF_NODES",
+            lambda s: NODE_COUNT_RE.fullmatch(s) is not None,
+            ["error: Enter a valid value (number between 1-9) or leave blank to use the default."])
+
+        public_at = 1
+        for var, message, first in (
+                ("RANCHER_MASTER_NETWORKS", "What networks should the master be a part of, provide comma separated values:", True),
+                ("KUBERNETES_NODE_NETWORKS", "What networks should the nodes be a part of, provide comma separated values:", False)):
+            self.echo(DASHES)
+            self.echo("From the networks below:")
+            count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None)
+            if first:
+                public_at = at
+            if v[var] == "":
+                v[var] = self.network_ids(self.args_of(str(public_at)))
+            self._prompt_index_list(var, message, count)
+
+        self.echo(DASHES)
+        self.echo("From the packages below:")
+        count, package_at = self._print_menu(packages, "k4-highcpu-kvm-7.75G=")
+        if v["HOST_PACKAGE"] == "":
+            v["HOST_PACKAGE"] = self.package_id(self.args_of(str(package_at)))
+        self._prompt_package(count)
+        v["HOST_PACKAGE"] = self.unq(v["HOST_PACKAGE"])
+
+    def _normalise_list(self, value: str) -> str:
+        """``echo $V | tr ',' '\\n' | sort | uniq | tr '\\n' ',' | sed 's/\\(.*\\),$/\\1/'``
+        -- lexical sort: ``10,2`` stays ``10,2`` (setup.sh:333-334)."""
+        t = tx.uniq(tx.sort_lines(tx.tr(sh.echo_unquoted(value, self.rt.root), ",", "\n")))
+        return sh.cmdsubst(tx.sed_sub(tx.tr(t, "\n", ","), r"^(.*),$", r"\1"))
+
+    def _out_of_range(self, items: List[str], count: int) -> int:
+        """How many of ``items`` fall outside 1..count (bash 64-bit arithmetic)."""
+        bad = 0
+        for item in items:
+            n = _to_int64(item)
+            if n > count or n < 1:
+                bad += 1
+        return bad
+
+    def _prompt_index_list(self, var: str, message: str, count: int) -> None:
+        v = self.v
+        errors = ["error: Enter a valid option or leave blank to use the default.",
+                  "    Values should be comma separated between 1 and %d." % count]
+        while True:
+            answer = self.get_argument(message, self.unq(v[var]))
+            v[var] = self._normalise_list(v[var])
+            answer = self._normalise_list(answer)
+            shown = sh.echo_unquoted(answer, self.rt.root)
+            if sh.cmdsubst(tx.grep(shown, INDEX_LIST_RE)) != "":
+                items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
+                bad = self._out_of_range(items, count)
+                for _ in range(bad):
+                    for line in errors:
+                        self.echo(line)
+                if bad == 0:
+                    v[var] = self.network_ids(self.args_of(answer))
+                    return
+            elif sh.pattern_match(answer, v[var]):
+                return  # the default UUID list was left as it is
+            else:
+                for line in errors:
+                    self.echo(line)
+
+    def _prompt_package(self, count: int) -> None:
+        v = self.v
+        errors = ["error: Enter a valid option or leave blank to use the default.",
+                  "    Value should be between 1 and %d." % count]
+        while True:
+            answer = self.get_argument("What KVM package should the master and nodes run on:", self.unq(v["HOST_PACKAGE"]))
+            shown = sh.echo_unquoted(answer, self.rt.root)
+            if sh.cmdsubst(tx.grep(shown, INDEX_RE)) != "":
+                items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
+                bad = self._out_of_range(items, count)
+                for _ in range(bad):
+                    for line in errors:
+                        self.echo(line)
+                if bad == 0:
+                    v["HOST_PACKAGE"] = self.package_id(self.args_of(answer))
+                    self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]))
+                    return
+            elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"])):
+                return
+            else:
+                for line in errors:
+                    self.echo(line)
+
+    # ------------------------------------------------------------------
+    # a5/a6  getNetworkIDs / getPackageID  (setup.sh:532-542)
+    # ------------------------------------------------------------------
+    def network_ids(self, args: List[str]) -> str:
+        """Index list -> UUID list, one ``triton networks`` call per index.  The
+        rows are sorted *raw* here but after the blank->'=' rewrite in the menu
+        (setup.sh:257 vs :536), which is the ordering hazard of SURVEY.md §7.4."""
+        arg1 = args[0] if args else ""
+        values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
+        acc = ""
+        for index in self.args_of(values):
+            _, text = self.rt.run(TRITON_NETWORKS, stdout=CAPTURE)
+            rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
+            acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
+        t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
+        return sh.cmdsubst(tx.sed_sub(t, r"^(.*),$", r"\1"))
+
+    def package_id(self, args: List[str]) -> str:
+        arg1 = args[0] if args else ""
+        _, text = self.rt.run(TRITON_PACKAGES, stdout=CAPTURE)
+        rows = tx.grep(tx.grep(text, r"-kvm-"), r"^NAME.*ID$", invert=True)
+        rows = tx.sort_lines(tx.tr_squeeze_spaces(rows))
+        picked = sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)))
+        return sh.cmdsubst(sh.echo_builtin([picked]))
+
+    def _nth_row(self, rows: str, index: str) -> str:
+        """``sed -n "${index}p"``."""
+        if not re.fullmatch(r"[0-9]+", index):
+            if index == "":
+                # `sed -n p` prints every row
+                return rows
+            self.rt.err("sed: -e expression #1, char %d: unknown command\n" % len(index))
+            return ""
+        return tx.sed_print_line(rows, int(index))
+
+    # ------------------------------------------------------------------
+    # a7  verifyConfig  (setup.sh:452-483)
+    # ------------------------------------------------------------------
+    def verify_config(self) -> None:
+        v = self.v
+        self.echo(RULE)
+        self.echo("Verify that the following configuration is correct:")
+        self.echo("")
+        self.echo("Name of kubernetes environment: %s" % v["KUBERNETES_NAME"])
+        self.echo("Kubernetes environment description: %s" % v["KUBERNETES_DESCRIPTION"])
+        self.echo("Master hostname: %s" % v["RANCHER_MASTER_HOSTNAME"])
+        self.echo("All node hostnames will start with: %s" % v["KUBERNETES_NODE_HOSTNAME_BEGINSWITH"])
+        self.echo("Kubernetes environment will have %s nodes" % v["KUBERNETES_NUMBER_OF_NODES"])
+        self.echo("Master server will be part of these networks: %s" % v["RANCHER_MASTER_NETWORKS"])
+        self.echo("Kubernetes nodes will be a part of these networks: %s" % v["KUBERNETES_NODE_NETWORKS"])
+        self.echo("This package will be used for all the hosts: %s" % v["HOST_PACKAGE"])
+        self.echo("")
+        self.echo("Make sure the above information is correct before answering:")
+        self.echo('    to view list of networks call "triton networks -l"')
+        self.echo('    to view list of packages call "triton packages -l"')
+        self.echo("WARN: Make sure that the nodes and master are part of networks that can communicate with each other and this system from which the setup is running.")
+        while True:
+            yn, ok = self.rt.read("Is the above config correct (yes | no)? ")
+            if not ok:
+                raise ScriptExit(1)  # read fails at EOF and errexit ends the run
+            if yn == "yes":
+                return
+            if yn == "no":
+                raise ScriptExit(0)  # ./config stays behind
+            self.echo("Please answer yes or no.")
+
+    # ------------------------------------------------------------------
+    # a8  setConfigToFile  (setup.sh:199-208)
+    # ------------------------------------------------------------------
+    def set_config_to_file(self) -> None:
+        v = self.v
+        for name in ("RANCHER_MASTER_NETWORKS", "KUBERNETES_NODE_NETWORKS", "KUBERNETES_NUMBER_OF_NODES"):
+            self.append_line("config", "%s=%s" % (name, v[name]))
+        for name in ("KUBERNETES_NAME", "KUBERNETES_DESCRIPTION", "RANCHER_MASTER_HOSTNAME",
+                     "KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "HOST_PACKAGE"):
+            self.append_line("config", '%s="%s"' % (name, v[name]))
+
+    # ------------------------------------------------------------------
+    # a9  exportVars  (setup.sh:543-549)
+    # ------------------------------------------------------------------
+    def export_vars(self) -> None:
+        """Every non-blank line of ./config is exported *verbatim*: values keep
+        their literal double quotes from here on, and each line
+        goes through ``read`` once more (backslashes processed again)."""
+        text = tx.grep(self.rt.read_text("config"), r"^$", invert=True)
+        data = sh.to_bytes(text)
+        pos = 0
+
+        def next_byte() -> Optional[int]:
+            nonlocal pos
+            if pos >= len(data):
+                return None
+            pos += 1
+            return data[pos - 1]
+
+        while True:
+            line, ok = sh.read_builtin(next_byte)
+            if not ok:
+                break
+            self._export(line)
+
+    def _export(self, word: str) -> None:
+        name, eq, value = word.partition("=")
+        append = name.endswith("+") and bool(eq)
+        if append:
+            name = name[:-1]
+        if not _IDENT.fullmatch(name):
+            self.rt.err("%s: line 546: export: `%s': not a valid identifier\n" % (self.program, word))
+            raise ScriptExit(1)
+        if eq:
+            self.v[name] = (self.v.get(name, "") + value) if append else value
+        if name in self.v:
+            self.rt.env[name] = self.v[name]
+
+    # ------------------------------------------------------------------
+    # a10-a13  Terraform root config + run  (setup.sh:138-198)
+    # ------------------------------------------------------------------
+    def run_terraform_tasks(self) -> None:
+        v, rt = self.v, self.rt
+        if rt.exists("terraform/rancher.tf"):
+            # unreachable from main (guarded earlier) but part of the function
+            self.echo("warning: a previous terraform configuration has been found")
+            self.echo("    skipping terraform configuration and execution...")
+            return
+        self.echo("Generating terraform configs for environment...")
+        self.update_terraform_config(["provider", "triton"])
+        self.echo("    Master hostname: %s" % v.get("RANCHER_MASTER_HOSTNAME", ""))  # quotes and all (setup.sh:146)
+        self.update_terraform_config(["master"] + self.args_of(self.unq(v.get("RANCHER_MASTER_HOSTNAME", ""))))
+        prefix = v.get("KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "")
+        i = 1
+        while i <= self._arith(v.get("KUBERNETES_NUMBER_OF_NODES", "")):
+            self.echo("    Kubernetes node %d: %s%d" % (i, self.unq(prefix), i))
+            self.update_terraform_config(["host"] + self.args_of(self.unq("%s%d" % (prefix, i))))
+            i += 1
+        self.echo("Starting terraform tasks")
+        self.must(rt.run(["terraform", "get"], cwd="terraform")[0])
+        self.must(rt.run(["terraform", "apply"], cwd="terraform")[0])
+        self.echo("    terraform tasks completed")
+
+    def _arith(self, text: str) -> int:
+        t = text.strip()
+        if re.fullmatch(r"[0-9]+", t):
+            return _to_int64(t)
+        if t == "":
+            return 0
+        self.rt.err("%s: ((: i <= %s: syntax error in expression\n" % (self.program, text))
+        raise ScriptExit(1)
+
+    def update_terraform_config(self, args: List[str]) -> None:
+        """One block of ``terraform/rancher.tf``.  ``provider`` truncates the
+        file, the module blocks append (setup.sh:162-198)."""
+        v = self.v
+        kind = args[0] if args else ""
+        label = args[1] if len(args) > 1 else ""
+        key = self.unq(v.get("SDC_KEY", ""))
+        rel = "terraform/rancher.tf"
+        if kind in ("master", "host"):
+            nets = v.get("RANCHER_MASTER_NETWORKS" if kind == "master" else "KUBERNETES_NODE_NETWORKS", "")
+            net_list = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(nets, self.rt.root), r",", '","', count=0))
+            block = [
+                "",
+                'module "%s" {' % label,
+                '    source = "%s"' % kind,
+                '    hostname = "%s"' % label,
+                '    networks = ["%s"]' % net_list,
+                '    root_authorized_keys = "${file("%s")}"' % key,   # the private key path: reference quirk, kept
+                '    package = "%s"' % self.unq(v.get("HOST_PACKAGE", "")),
+                "}",
+            ]
+            for line in block:
+                self.append_line(rel, line)
+            return
+        if kind == "provider":
+            block = [
+                'provider "triton" {',
+                '    account = "%s"' % self.unq(v.get("SDC_ACCOUNT", "")),
+                '    key_material = "${file("%s")}"' % key,
+                '    key_id = "%s"' % self.unq(v.get("SDC_KEY_ID", "")),
+                '    url = "%s"' % self.unq(v.get("SDC_URL", "")),
+                "}",
+            ]
+            try:
+                self.rt.write_text(rel, sh.echo_builtin([block[0]]))
+            except OSError as exc:
+                self._redirect_failed(rel, exc)
+            for line in block[1:]:
+                self.append_line(rel, line)
+            return
+        self.echo("error: problem updating terraform configuration...")
+        raise ScriptExit(1)
+
+    # ------------------------------------------------------------------
+    # a15  createAnsibleConfigs  (setup.sh:116-137)
+    # ------------------------------------------------------------------
+    def create_ansible_configs(self) -> None:
+        rt, v = self.rt, self.v
+        if not rt.exists("terraform/masters.ip") or not rt.exists("terraform/hosts.ip"):
+            self.echo("Terraform had too many errors. Make sure you haven't reached your provisioning limit.")
+            raise ScriptExit(1)
+        self.echo("Creating ansible hosts file and variable files")
+        hosts = "ansible/hosts"
+        if rt.exists(hosts):
+            os.remove(rt.path(hosts))
+        self.append_line(hosts, "[MASTER]")
+        rt.append_text(hosts, rt.read_text("terraform/masters.ip"))
+        self.append_line(hosts, "[HOST]")
+        rt.append_text(hosts, rt.read_text("terraform/hosts.ip"))
+        self.echo("    created: ansible/hosts")
+
+        vars_yml = "ansible/roles/ranchermaster/vars/vars.yml"
+        master = sh.cmdsubst(tx.tail_1(rt.read_text("terraform/masters.ip")))
+        try:
+            rt.write_text(vars_yml, sh.echo_builtin(["master: %s" % master]))
+        except OSError as exc:
+            self._redirect_failed(vars_yml, exc)
+        self.append_line(vars_yml, 'kubernetes_name: "%s"' % self.unq(v.get("KUBERNETES_NAME", "")))
+        self.append_line(vars_yml, 'kubernetes_description: "%s"' % self.unq(v.get("KUBERNETES_DESCRIPTION", "")))
+
+        self._rewrite_private_key_file("ansible/ansible.cfg", "ansible/tmp.cfg", ";", self.unq(v.get("SDC_KEY", "")),
+                                       shown_src="ansible.cfg")
+        self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml")
+
+    def _rewrite_private_key_file(self, cfg: str, tmp: str, delim: str, value: str, shown_src: str) -> None:
+        """``sed "s<d>private_key_file = .*$<d>private_key_file = VALUE<d>g" cfg > tmp && mv tmp cfg``
+        (setup.sh:133 with ';', setup.sh:511 with '~').  VALUE is spliced into the sed
+        program text, so sed's own replacement syntax applies to it."""
+        rt = self.rt
+        repl = _sed_replacement(value, delim)
+        try:
+            rt.write_text(tmp, "")  # the redirection creates/truncates the target first
+        except OSError as exc:
+            rt.err("%s: %s: %s\n" % (self.program, tmp, exc.strerror))
+            return
+        if repl is None:
+            rt.err("sed: -e expression #1, char %d: unknown option to `s'\n" % (len(value) + 40))
+            return
+        try:
+            text = rt.read_text(cfg)
+        except OSError as exc:
+            rt.err("sed: can't read %s: %s\n" % (shown_src, exc.strerror))
+            return
+        rt.write_text(tmp, tx.sed_sub(text, r"private_key_file = .*$", lambda m: repl(m.group(0)), count=0))
+        os.replace(rt.path(tmp), rt.path(cfg))
+
+    # ------------------------------------------------------------------
+    # runAnsible  (setup.sh:111-115)
+    # ------------------------------------------------------------------
+    def run_ansible(self) -> None:
+        if not os.path.isdir(self.rt.path("ansible")):
+            self.rt.err("%s: line 112: cd: ansible: No such file or directory\n" % self.program)
+            raise ScriptExit(1)
+        self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible")[0])
+
+    # ------------------------------------------------------------------
+    # dashboard wait loop  (setup.sh:59-85)
+    # ------------------------------------------------------------------
+    def _dashboard_url_words(self) -> List[str]:
+        """``http://$(cat terraform/masters.ip):8080/r/projects/$(cat …id)/kubernetes-dashboard:9090/``
+        as an unquoted word."""
+        return sh.expand_word([
+            ("http://", False), (self.cat_subst("terraform/masters.ip"), True),
+            (":8080/r/projects/", False), (self.cat_subst("ansible/tmp/kubernetes_environment.id"), True),
+            ("/kubernetes-dashboard:9090/", False)], self.rt.root)
+
+    def _curl_dashboard(self) -> Tuple[int, str]:
+        return self.rt.run(["curl", "--connect-timeout", "5", "--max-time", "5", "-s"] + self._dashboard_url_words(),
+                           stdout=CAPTURE)
+
+    def _ssh_docker_ps(self, node: str) -> str:
+        return self.rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node, "docker", "ps"],
+                           stdout=CAPTURE)[1]
+
+    def wait_for_dashboard(self) -> None:
+        """Poll once a second; every time the epoch is a multiple of 15 ask the
+        dashboard URL.  A body mentioning "kubernetes" ends the wait.  Otherwise,
+        when the nodes run exactly two dashboard containers and the proxy
+        answers "Service Unavailable", stop the stuck pod container on every
+        node that has one (upstream-bug workaround, setup.sh:69-82)."""
+        rt = self.rt
+        up = False
+        while not up:
+            rt.out(".")
+            self.must(rt.sleep(1))
+            now = sh.cmdsubst(rt.epoch())
+            if not re.fullmatch(r"[0-9]+", now) or int(now) % 15 != 0:
+                continue
+            status, body = self._curl_dashboard()
+            self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
+            shown = sh.echo_unquoted(sh.cmdsubst(body), rt.root)
+            if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True)) != 0:
+                up = True
+                continue
+            count = 0
+            for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
+                ps = tx.grep(self._ssh_docker_ps(node), r"kubernetes-dashboard")
+                count += tx.wc_w(tx.awk_print_field(ps, 1))
+            if count != 2:
+                continue
+            _, body = self._curl_dashboard()
+            if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True)) == 0:
+                continue
+            for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
+                ps = tx.grep(self._ssh_docker_ps(node), r"k8s_POD.*dashboard")
+                container = sh.cmdsubst(tx.awk_print_field(ps, 1))
+                if container != "":
+                    status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,
+                                        "docker stop -t0 %s" % container], stdout=DEVNULL, stderr=DEVNULL)
+                    self.must(status)
+                rt.out(".")
+
+    # ------------------------------------------------------------------
+    # cleanRunner  (setup.sh:484-521)
+    # ------------------------------------------------------------------
+    def clean_runner(self) -> None:
+        rt = self.rt
+        self.echo("Clearing settings....")
+        while True:
+            if rt.exists("terraform/masters.ip"):
+                self.echo("WARNING: You are about to destroy the following KVMs associated with Rancher cluster:")
+                try:
+                    rt.out(rt.read_text("terraform/masters.ip"))
+                except OSError:
+                    raise ScriptExit(1)
+                try:
+                    rt.out(rt.read_text("terraform/hosts.ip"))
+                except OSError:
+                    raise ScriptExit(1)  # `cat … 2>/dev/null` still fails, errexit
+                yn, ok = rt.read("Do you wish to destroy the KVMs and reset configuration (yes | no)? ")
+            else:
+                yn, ok = rt.read("Do you wish to reset configuration (yes | no)? ")
+            if not ok:
+                raise ScriptExit(1)
+            if yn == "yes":
+                self._clean()
+                self.echo("    All clear!")
+                return
+            if yn == "no":
+                raise ScriptExit(0)
+            self.echo("Please answer yes or no.")
+
+    def _clean(self) -> None:
+        rt = self.rt
+        if rt.exists("terraform/rancher.tf"):
+            self.echo("    destroying images...")
+            rt.run(["terraform", "destroy", "-force"], cwd="terraform", stderr=DEVNULL)  # `|| true`
+        if (rt.exists("terraform/hosts.ip") and rt.exists("terraform/masters.ip")
+                and os.path.exists(self.tilde("~/.ssh/known_hosts"))):
+            recorded = sh.cmdsubst(rt.read_text("terraform/hosts.ip") + rt.read_text("terraform/masters.ip"))
+            for host_key in self.args_of(recorded):
+                # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped
+                status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT)
+                self.must(status)
+        for rel in ("terraform/hosts.ip", "terraform/masters.ip", "terraform/rancher.tf"):
+            _rm_rf(rt.path(rel))
+        for pattern in ("terraform/terraform.*", "terraform/.terraform*"):
+            for rel in sh.glob_word(pattern, rt.root):
+                _rm_rf(rt.path(rel))
+        self._rewrite_private_key_file("ansible/ansible.cfg", "tmp", "~", "", shown_src="ansible/ansible.cfg")
+        for rel in ["ansible/hosts", "ansible/ansible.cfg.tmp"] + sh.glob_word("ansible/*retry", rt.root):
+            p = rt.path(rel)
+            if os.path.isfile(p) or os.path.islink(p):
+                os.remove(p)
+            elif os.path.isdir(p):
+                rt.err("rm: cannot remove '%s': Is a directory\n" % rel)
+        _rm_rf(rt.path("config"))
+        for rel in sh.glob_word("tmp/*", rt.root):
+            _rm_rf(rt.path(rel))
+
+
+def _rm_rf(path: str) -> None:
+    if os.path.isdir(path) and not os.path.islink(path):
+        shutil.rmtree(path, ignore_errors=True)
+    elif os.path.lexists(path):
+        try:
+            os.remove(path)
+        except OSError:
+            pass
+
+
+def _sed_replacement(value: str, delim: str) -> Optional[Callable[[str], str]]:
+    """Interpret VALUE as the replacement half of a sed ``s`` command whose
+    delimiter is ``delim``.  Returns a function matched-text -> replacement, or
+    None when VALUE makes the sed program invalid (unescaped delimiter/newline)."""
+    parts: List[Tuple[str, str]] = []
+    i, n = 0, len(value)
+    while i < n:
+        c = value[i]
+        if c == "\\" and i + 1 < n:
+            d = value[i + 1]
+            i += 2
+            if d == "n":
+                parts.append(("lit", "\n"))
+            elif d in "123456789":
+                return None  # reference to a group the expression does not have
+            elif d == "0":
+                parts.append(("match", ""))
+            else:
+                parts.append(("lit", d))
+            continue
+        if c == delim or c == "\n":
+            return None
+        if c == "&":
+            parts.append(("match", ""))
+        else:
+            parts.append(("lit", c))
+        i += 1
+
+    def render(matched: str) -> str:
+        return "private_key_file = " + "".join(matched if k == "match" else t for k, t in parts)
+    return render

@@ -1,0 +1,127 @@
+"""Line tools of the path (``grep``, ``sed``, ``tr``, ``sort``, ``uniq``, ``awk``,
+``tail``) restated as functions on text, C locale.
+
+Each function takes the bytes a pipeline stage would read (as ``str``) and
+returns the bytes it would write, so a pipeline of the reference reads here as a
+chain of calls in the same order.  Only the option/flag combinations the
+reference uses are covered (cited per function).
+"""
+from __future__ import annotations
+
+import re
+from typing import Callable, List
+
+from .bashsem import c_sort_key
+
+
+def lines(text: str) -> List[str]:
+    """Records as a line-oriented tool sees them (a last unterminated line counts)."""
+    if text == "":
+        return []
+    ls = text.split("\n")
+    if ls[-1] == "":
+        ls.pop()
+    return ls
+
+
+def unlines(ls: List[str]) -> str:
+    return "".join(l + "\n" for l in ls)
+
+
+def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = False) -> str:
+    """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE."""
+    rx = re.compile(pattern, re.I if ignore_case else 0)
+    return unlines([l for l in lines(text) if (rx.search(l) is not None) != invert])
+
+
+def tr_squeeze_spaces(text: str) -> str:
+    """``tr -s " "`` (setup.sh:257,259,541)."""
+    return re.sub(r" +", " ", text)
+
+
+def tr(text: str, a: str, b: str) -> str:
+    """``tr A B`` for single characters (setup.sh:257,334,533)."""
+    return text.replace(a, b)
+
+
+def sort_lines(text: str) -> str:
+    """``sort`` under LC_ALL=C (setup.sh:257,334,536)."""
+    return unlines(sorted(lines(text), key=c_sort_key))
+
+
+def uniq(text: str) -> str:
+    """``uniq`` (setup.sh:334)."""
+    out: List[str] = []
+    for l in lines(text):
+        if not out or out[-1] != l:
+            out.append(l)
+    return unlines(out)
+
+
+def sed_sub(text: str, pattern: str, repl, count: int = 1) -> str:
+    """``sed 's/PATTERN/REPL/[g]'`` line by line; ``count=0`` is the ``g`` flag.
+    GNU sed keeps a missing final newline missing."""
+    rx = re.compile(pattern)
+    ls = text.split("\n")
+    tail_nl = ls[-1] == ""
+    if tail_nl:
+        ls.pop()
+    out = "\n".join(rx.sub(repl, l, count=count) for l in ls)
+    if text == "":
+        return ""
+    return out + ("\n" if tail_nl else "")
+
+
+def strip_dquotes(text: str) -> str:
+    """``sed 's/"//g'`` -- the quote-stripper used at 15+ sites (e.g. setup.sh:130)."""
+    return text.replace('"', "")
+
+
+def sed_print_line(text: str, n: int) -> str:
+    """``sed -n "${n}p"`` (setup.sh:536,541)."""
+    ls = lines(text)
+    if 1 <= n <= len(ls):
+        return ls[n - 1] + "\n"
+    return ""
+
+
+def _awk_fields(line: str) -> List[str]:
+    return [f for f in re.split(r"[ \t]+", line) if f]
+
+
+def awk_print_field(text: str, idx: int) -> str:
+    """``awk '{print $idx}'`` (setup.sh:68,72,217)."""
+    out = []
+    for l in lines(text):
+        f = _awk_fields(l)
+        out.append(f[idx - 1] if len(f) >= idx else "")
+    return unlines(out)
+
+
+def awk_last_field_if_many(text: str) -> str:
+    """``awk 'NF>1{print $NF}'`` (setup.sh:536,541)."""
+    out = []
+    for l in lines(text):
+        f = _awk_fields(l)
+        if len(f) > 1:
+            out.append(f[-1])
+    return unlines(out)
+
+
+def tail_1(text: str) -> str:
+    """``tail -1`` (setup.sh:127)."""
+    if text == "":
+        return ""
+    body = text[:-1] if text.endswith("\n") else text
+    last = body.rsplit("\n", 1)[-1]
+    return last + ("\n" if text.endswith("\n") else "")
+
+
+def wc_l(text: str) -> int:
+    """``wc -l``: newline count."""
+    return text.count("\n")
+
+
+def wc_w(text: str) -> int:
+    """``wc -w``."""
+    return len([w for w in re.split(r"[ \t\n\r\f\v]+", text) if w])
