@@ -1,0 +1,221 @@
+"""The scenario catalogue: BASELINE.json's five configs plus the edge cases the
+path has (SURVEY.md §5 validation table, §7.4 hard parts, §8d negative sub-cases).
+
+``CONFIGS`` are the five scored configurations.  ``EDGE`` are
+parity cases: every branch of the prompt validation, the guards, the failure
+exits, the clean path and the dashboard wait loop.  The reference has no tests
+(SURVEY.md §4), so each edge case cites the script lines it exercises instead of
+a reference test.
+"""
+from __future__ import annotations
+
+from typing import Dict, List
+
+from .scenario import (DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario,
+                       triton_env_text, triton_table)
+
+YES = "yes\n"
+BLANK8 = "\n" * 8
+
+
+def _answers(*lines: str) -> str:
+    return "".join(l + "\n" for l in lines)
+
+
+# ---------------------------------------------------------------------------
+# the five BASELINE.json configs
+# ---------------------------------------------------------------------------
+CONFIGS: List[Scenario] = [
+    Scenario(name="config1_defaults_1worker", stdin=BLANK8 + YES,
+             note="BASELINE config 1: every prompt left at its default"),
+    Scenario(name="config2_quickstart_2workers", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             note="BASELINE config 2: README.md:112-121 answers"),
+    Scenario(name="config3_custom_names_multinet",
+             stdin=_answers("prod k8s", 'my "quoted" desc', "km01", "wrk", "3", "4,2,2", "1,3", "1", "yes"),
+             note="BASELINE config 3: custom hostname + prefix + several networks (sorted, de-duplicated)"),
+    Scenario(name="config4_5workers_inventory", stdin=_answers("", "", "", "", "5", "", "", "", "yes"),
+             note="BASELINE config 4: 5 workers, inventory render"),
+    Scenario(name="config5_10workers_rejected_then_9", stdin=_answers("", "", "", "", "10", "9", "", "", "", "yes"),
+             note="BASELINE config 5: 10 is outside the reference's domain (setup.sh:301); 9 is the maximum"),
+]
+
+# ---------------------------------------------------------------------------
+# edge cases
+# ---------------------------------------------------------------------------
+_TWELVE_NETWORKS = [("net%02d" % i, "00000000-0000-0000-0000-%012d" % i) for i in range(1, 13)]
+_COLLIDING_NETWORKS = [("kube", "aaaaaaaa-0000-0000-0000-000000000001"),
+                       ("kube-net", "bbbbbbbb-0000-0000-0000-000000000002"),
+                       ("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4")]
+_COLLIDING_PACKAGES = [("k4-kvm-1G", "cccccccc-0000-0000-0000-000000000001"),
+                       ("k4-kvm-1G-kvm-x", "dddddddd-0000-0000-0000-000000000002"),
+                       ("k4-highcpu-kvm-7.75G", "14b6fade-d0f8-11e5-85c5-4ff7918ab5c1")]
+
+_RAN_FILES: Dict[str, str] = {
+    "config": "ANSIBLE_HOST_KEY_CHECKING=False\nSDC_URL=\"x\"\n",
+    "terraform/rancher.tf": 'provider "triton" {\n}\n',
+    "terraform/masters.ip": "10.0.0.1\n",
+    "terraform/hosts.ip": "10.0.1.1\n10.0.1.2\n",
+    "terraform/terraform.tfstate": "{}\n",
+    "terraform/terraform.tfstate.backup": "{}\n",
+    "terraform/.terraform/modules/abc/main.tf": "# fetched module\n",
+    "ansible/hosts": "[MASTER]\n10.0.0.1\n[HOST]\n10.0.1.1\n10.0.1.2\n",
+    "ansible/clusterUp.retry": "10.0.1.2\n",
+    "ansible/ansible.cfg.tmp": "stale\n",
+    "tmp/scratch.txt": "scratch\n",
+    "tmp/sub/deep.txt": "deep\n",
+}
+
+_PS_TWO_DASHBOARDS = (
+    "CONTAINER ID        IMAGE                                  COMMAND        NAMES\n"
+    "1111aaaa2222        gcr.io/kubernetes-dashboard-amd64:v1   \"/dashboard\"   k8s_kubernetes-dashboard.abc\n"
+    "3333bbbb4444        gcr.io/pause-amd64:3.0                 \"/pause\"       k8s_POD.d8dbe16c_kubernetes-dashboard-716739405\n"
+    "5555cccc6666        rancher/agent:v1.2.0                   \"/run.sh\"      rancher-agent\n")
+_PS_NONE = (
+    "CONTAINER ID        IMAGE                                  COMMAND        NAMES\n"
+    "5555cccc6666        rancher/agent:v1.2.0                   \"/run.sh\"      rancher-agent\n")
+
+EDGE: List[Scenario] = [
+    # --- prompt validation (setup.sh:273-307) --------------------------------
+    Scenario(name="bad_hostnames", stdin=_answers("", "", "1bad", "a", "has-dash", "km", "x_y", "9n", "n0", "", "", "", "", "yes"),
+             note="hostname/prefix regex ^[a-zA-Z][0-9a-zA-Z]+$ incl. the 1-char rejection"),
+    Scenario(name="bad_node_counts", stdin=_answers("", "", "", "", "0", "10", "x", "1 2", "", "", "", "", "yes"),
+             note="node count regex ^[1-9]$"),
+    # --- network selection (setup.sh:309-400) --------------------------------
+    Scenario(name="net_out_of_range", stdin=_answers("", "", "", "", "", "5", "0", "1,9", "007", "2,", ",2", "x", "3", "4,4,4", "", "yes"),
+             note="index range checks and the index-list regex"),
+    Scenario(name="net_lexical_sort", networks=triton_table(_TWELVE_NETWORKS),
+             stdin=_answers("", "", "", "", "", "10,2", "9,10,11", "", "yes"),
+             note="sort without -n: 10,2 stays 10,2 (SURVEY §7.4)"),
+    Scenario(name="net_with_blanks", stdin=_answers("", "", "", "", "", "2, 4", "4 ,2", " 3 ", "", "yes"),
+             note="blanks inside the index list: what echo's field splitting makes of them"),
+    Scenario(name="net_prefix_collision", networks=triton_table(_COLLIDING_NETWORKS),
+             stdin=_answers("", "", "", "", "", "2", "3", "", "yes"),
+             note="menu order != resolver order when one name is a '-' extension of another (SURVEY §7.4)"),
+    Scenario(name="net_uuid_typed_in", stdin=_answers("", "", "", "", "", "31428241-4878-47d6-9fba-9a8436b596a4", "deadbeef", "", "", "yes"),
+             note="typing the default UUID is accepted by the [[ == ]] branch; any other string is not"),
+    Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
+             stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
+    Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),
+             note="one network: index 2 is out of range"),
+    Scenario(name="net_empty_table", networks="NAME  ID\n", stdin=BLANK8 + YES,
+             note="no networks at all: empty default, everything still flows"),
+    # --- package selection (setup.sh:401-450) --------------------------------
+    Scenario(name="pkg_out_of_range", stdin=_answers("", "", "", "", "", "", "", "19", "0", "1,2", "abc", "10", "yes"),
+             note="package index checks; prints 'entered 10 and got <uuid>'"),
+    Scenario(name="pkg_default_missing", packages=triton_table(DOC_PACKAGES[:13] + NON_KVM_PACKAGES),
+             stdin=BLANK8 + YES, note="no k4-highcpu-kvm-7.75G row: default position 1 (setup.sh:404)"),
+    Scenario(name="pkg_prefix_collision", packages=triton_table(_COLLIDING_PACKAGES),
+             stdin=_answers("", "", "", "", "", "", "", "1", "yes"),
+             note="menu sorted after blank->'=', resolver sorted with blanks kept (setup.sh:259 vs :541)"),
+    Scenario(name="pkg_huge_index", stdin=_answers("", "", "", "", "", "", "", "99999999999999999999", "18446744073709551617", "yes"),
+             note="64-bit wrap-around of bash arithmetic in the range check"),
+    # --- free text and quoting ---------------------------------
+    Scenario(name="text_quotes_and_blanks", stdin=_answers('  spaced   out  ', 'say "hi"  twice', "", "", "", "", "", "", "yes"),
+             note="field splitting collapses blanks; quotes survive in config, not in vars.yml"),
+    Scenario(name="text_backslashes", stdin=_answers("back\\\\slash", "tab\\there c:\\\\dir\\\\", "", "", "", "", "", "", "yes"),
+             note="read without -r, twice (prompt and exportVars)"),
+    Scenario(name="text_glob_chars", stdin=_answers("*", "terraform/* ? [a-z]*", "", "", "", "", "", "", "yes"),
+             note="unquoted echo pathname-expands the answer against the workspace"),
+    Scenario(name="text_echo_options", stdin=_answers("-n", "-e a\\\\tb", "", "", "", "", "", "", "yes"),
+             note="a leading -n/-e in the answer is taken by echo as an option"),
+    Scenario(name="text_shell_metachars", stdin=_answers("$HOME `id` $(id)", "a;b|c&d>e<f 'q' ~ #x", "", "", "", "", "", "", "yes"),
+             note="nothing is evaluated: the answers are data"),
+    Scenario(name="text_utf8", stdin=_answers("café ☕", "naïve — test", "", "", "", "", "", "", "yes"),
+             note="non-ASCII bytes pass through untouched under LC_ALL=C"),
+    Scenario(name="text_embedded_newline", stdin=_answers("-e a\\\\nb", "", "", "", "", "", "", "", "yes"),
+             note="echo -e turns the answer into two lines; exportVars then dies on `b\"` (exit 1, config.tmp left)"),
+    Scenario(name="text_nul_and_c_escape", stdin=_answers("-e a\\\\0b", "-e cut\\\\chere", "", "", "", "", "", "", "yes"),
+             note="\\0 makes a NUL that $(...) drops with a warning on stderr; \\c cuts the output"),
+    Scenario(name="text_line_continuation", stdin="first\\\nsecond\n" + "\n" * 7 + YES,
+             note="backslash-newline joins two input lines (read without -r)"),
+    Scenario(name="text_crlf_answers", stdin="name\r\n\r\n\r\n\r\n2\r\n\r\n\r\n\r\nyes\r\nyes\n",
+             note="CR is data: 'km\\r' style answers fail the regexes, '\\r' is not the empty answer"),
+    Scenario(name="idx_echo_options", stdin=_answers("", "", "", "", "", "-n 4", "-e 1\\\\n2", "-n 4", "", "yes"),
+             note="-n/-e in an index answer: what grep sees differs from what the resolver gets"),
+    # --- confirmation (setup.sh:471-482) --------------------------------------
+    Scenario(name="verify_no", stdin=BLANK8 + "no\n", note="'no' exits 0 and leaves ./config behind"),
+    Scenario(name="verify_garbage_then_yes", stdin=BLANK8 + _answers("maybe", "YES", "y", "", " yes ", "yes"),
+             note="only exact yes/no; ' yes ' is trimmed by read and accepted"),
+    Scenario(name="verify_eof", stdin=BLANK8, note="EOF at the confirmation: read fails, errexit, status 1"),
+    Scenario(name="stdin_empty", stdin="", note="every prompt at EOF takes its default; dies at the confirmation"),
+    Scenario(name="stdin_no_final_newline", stdin=BLANK8 + "yes", note="'yes' without newline: read returns 1 -> exit 1"),
+    # --- guards (setup.sh:14-18, 241-244) -------------------------------------
+    Scenario(name="guard_previous_run", stdin=BLANK8 + YES, pre_files={"terraform/rancher.tf": "# left over\n"},
+             note="previous-run guard: message and exit 0"),
+    Scenario(name="guard_stale_config_clean_yes", stdin="yes\n" + BLANK8 + YES, pre_files={"config": "OLD=1\n"},
+             note="stale ./config: cleanRunner consumes one extra answer, then the run proceeds"),
+    Scenario(name="guard_stale_config_clean_no", stdin="no\n" + BLANK8 + YES, pre_files={"config": "OLD=1\n"},
+             note="stale ./config, operator declines: exit 0"),
+    # --- key discovery (setup.sh:215-238) --------------------------------------
+    Scenario(name="key_not_found_then_clean", stdin="yes\n", keygen={"id_rsa": "2048 MD5:ff:ff:ff:ff other (RSA)\n"},
+             note="fingerprint mismatch: message, cleanRunner, exit 1"),
+    Scenario(name="key_not_found_decline_clean", stdin="no\n", keygen={"id_rsa": "2048 MD5:ff:ff:ff:ff other (RSA)\n"},
+             note="fingerprint mismatch, decline clean: exit 0 with ./config left"),
+    Scenario(name="key_legacy_ssh_keygen", stdin=BLANK8 + YES, keygen_no_E=True, keygen={},
+             keygen_legacy={"id_rsa": "2048 %s fixture@host (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={},
+             note="ssh-keygen without -E prints MD5 by default (setup.sh:222-229)"),
+    Scenario(name="key_among_other_files", stdin=BLANK8 + YES,
+             ssh_files={"authorized_keys": "ssh-rsa AAAA\n", "config": "Host *\n", "github_rsa": "K\n", "github_rsa.pub": "P\n",
+                        "id_rsa": "K\n", "id_rsa.pub": "P\n", "known_hosts": "h\n"},
+             keygen={"github_rsa": "4096 MD5:11:22:33:44 gh (RSA)\n", "id_rsa": "2048 MD5:%s fixture@host (RSA)\n" % DEFAULT_KEY_ID},
+             keygen_sha={"github_rsa": "4096 SHA256:zzzz gh (RSA)\n", "id_rsa": "2048 SHA256:yyyy x (RSA)\n"},
+             note="~/.ssh walked in ls order; non-key files cost two failed ssh-keygen calls each"),
+    Scenario(name="key_pub_suffix_sed", stdin=BLANK8 + YES,
+             ssh_files={"mykey.pub": "P\n", "mykey": "K\n"},
+             keygen={"mykey": "2048 MD5:%s fixture@host (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={"mykey": "2048 SHA256:q x (RSA)\n"},
+             note="the .pub suffix is stripped before ssh-keygen is asked (setup.sh:217)"),
+    Scenario(name="key_no_ssh_dir_entries", stdin="yes\n", ssh_files={}, note="empty ~/.ssh: key not found"),
+    Scenario(name="triton_env_fails", stdin="yes\n", fail={"triton-env": 1},
+             note="triton env failing is swallowed by eval \"$(...)\"; empty SDC_* then matches the first non-key"),
+    # --- below the offline line (setup.sh:117-120,154-159,113) ----------------
+    Scenario(name="terraform_get_fails", stdin=BLANK8 + YES, fail={"terraform-get": 3}, note="errexit with terraform's status"),
+    Scenario(name="terraform_apply_fails", stdin=BLANK8 + YES, fail={"terraform-apply": 1}, note="errexit with terraform's status"),
+    Scenario(name="terraform_writes_no_ips", stdin=BLANK8 + YES, terraform_no_ips=True,
+             note="provisioning limit: 'Terraform had too many errors', exit 1 (setup.sh:117-120)"),
+    Scenario(name="ansible_fails", stdin=BLANK8 + YES, fail={"ansible-playbook--i": 2}, note="errexit with ansible-playbook's status"),
+    Scenario(name="ansible_cfg_missing", stdin=BLANK8 + YES, pre_remove=["ansible/ansible.cfg"],
+             note="sed cannot read ansible.cfg: '&&' list fails quietly, tmp.cfg is left behind"),
+    Scenario(name="env_id_from_playbook", stdin=_answers("", "", "", "", "2", "", "", "", "yes"), env_id="1a9", master_ip="165.225.1.2",
+             note="banner URLs come from masters.ip and the id the playbook stored"),
+    Scenario(name="env_id_missing", stdin=BLANK8 + YES, pre_remove=["ansible/tmp/kubernetes_environment.id"],
+             note="no stored id: cat fails inside $(...), URLs have an empty id"),
+    # --- dashboard wait loop (setup.sh:59-85) ---------------------------------
+    Scenario(name="wait_not_on_15s_boundary", stdin=BLANK8 + YES, date_seq=["1500000001", "1500000002", "1500000014"],
+             note="curl is only tried when epoch % 15 == 0"),
+    Scenario(name="wait_not_ready_then_up", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             curl_seq=["<html>starting</html>\n", "", "<title>KUBERNETES dashboard</title>\n"],
+             ssh_ps={"10.0.1.1": _PS_NONE, "10.0.1.2": _PS_NONE},
+             note="not ready: count dashboard containers over ssh on every node, keep polling"),
+    Scenario(name="wait_stuck_dashboard_killed", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             curl_seq=["503 Service Unavailable\n", "503 service unavailable\n", "<title>Kubernetes Dashboard</title>\n"],
+             ssh_ps={"10.0.1.1": _PS_TWO_DASHBOARDS, "10.0.1.2": _PS_NONE},
+             note="exactly two dashboard containers + Service Unavailable: docker stop -t0 the pod container"),
+    Scenario(name="wait_two_containers_but_other_error", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             curl_seq=["502 Bad Gateway\n", "502 Bad Gateway\n", "kubernetes\n"],
+             ssh_ps={"10.0.1.1": _PS_TWO_DASHBOARDS, "10.0.1.2": _PS_NONE},
+             note="two containers but not 'Service Unavailable': nothing is stopped"),
+    Scenario(name="wait_ssh_fails", stdin=BLANK8 + YES, curl_seq=["nope\n", "kubernetes\n"], ssh_exit={"10.0.1.1": 255},
+             note="ssh failures while counting are swallowed by '|| true'"),
+    Scenario(name="wait_curl_fails", stdin=BLANK8 + YES, fail={"curl---connect-timeout": 7},
+             note="cRetVal=$(curl …) under errexit: a refused connection ends the script with curl's status"),
+    # --- clean (setup.sh:484-521) ----------------------------------------------
+    Scenario(name="clean_fresh_yes", args=["-c"], stdin="yes\n", note="nothing to clean: still rewrites ansible.cfg"),
+    Scenario(name="clean_fresh_no", args=["-c"], stdin="no\n", note="decline: exit 0"),
+    Scenario(name="clean_garbage_then_yes", args=["-c"], stdin="y\nYes\n\nyes\n", note="re-prompts until yes/no"),
+    Scenario(name="clean_eof", args=["-c"], stdin="", note="EOF at the clean prompt: exit 1"),
+    Scenario(name="clean_after_run", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES, known_hosts="10.0.0.1 ssh-rsa AAAA\n",
+             note="full lifecycle: terraform destroy, known_hosts scrub, every generated file removed; ansible/tmp survives"),
+    Scenario(name="clean_after_run_no_known_hosts", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES,
+             note="without ~/.ssh/known_hosts no ssh-keygen -R calls"),
+    Scenario(name="clean_destroy_fails", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES, fail={"terraform-destroy": 1},
+             note="terraform destroy errors are swallowed (|| true)"),
+    Scenario(name="clean_masters_without_hosts", args=["-c"], stdin="yes\n", pre_files={"terraform/masters.ip": "10.0.0.1\n"},
+             note="masters.ip without hosts.ip: `cat hosts.ip` fails under errexit before the prompt"),
+    Scenario(name="clean_keygen_R_fails", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES, known_hosts="x\n", fail={"ssh-keygen--R": 1},
+             note="ssh-keygen -R failing ends the clean half-way (errexit)"),
+    Scenario(name="clean_other_arg_ignored", args=["--clean"], stdin=BLANK8 + YES, note="only -c means clean; anything else is a normal run"),
+]
+
+ALL: List[Scenario] = CONFIGS + EDGE
+BY_NAME: Dict[str, Scenario] = {s.name: s for s in ALL}
+assert len(BY_NAME) == len(ALL), "duplicate scenario names"

@@ -1,0 +1,65 @@
+"""Replay a golden fixture against an implementation of the path.
+
+A golden fixture (tests/golden/*.json, written by oracle/make_golden.py) carries
+everything needed to reproduce the recorded run without the reference tree: the
+scenario, the contents of the few static files the path reads, and the *names*
+of the files in the workspace (free-text answers are pathname-expanded against
+them).  Replay builds that skeleton, runs the implementation in the sandbox and
+returns both observations.
+"""
+from __future__ import annotations
+
+import json
+import os
+import shutil
+import sys
+import tempfile
+from typing import Dict, List, Optional, Sequence, Tuple
+
+from .sandbox import Observation, Sandbox
+from .scenario import Scenario
+
+PACKAGE_PARENT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+#: how the replacement is invoked inside the sandbox (cwd = workspace root)
+REPLACEMENT_ARGV = [sys.executable, "-m", "tritonk8ssupervisor_b200"]
+REPLACEMENT_ENV = {"PYTHONPATH": PACKAGE_PARENT, "TK8S_EXTERNAL_CLOCK": "1", "PYTHONDONTWRITEBYTECODE": "1"}
+
+
+def load_golden(path: str) -> dict:
+    with open(path, encoding="utf-8") as fh:
+        return json.load(fh)
+
+
+def golden_dir() -> str:
+    return os.path.join(PACKAGE_PARENT, "tests", "golden")
+
+
+def list_goldens(directory: Optional[str] = None) -> List[str]:
+    d = directory or golden_dir()
+    return sorted(os.path.join(d, f) for f in os.listdir(d) if f.endswith(".json"))
+
+
+def build_skeleton(doc: dict, dest: str) -> str:
+    """Workspace with the recorded path listing (empty files) and input contents."""
+    for rel in doc["workspace_listing"]:
+        p = os.path.join(dest, rel)
+        os.makedirs(os.path.dirname(p), exist_ok=True)
+        with open(p, "w", encoding="utf-8") as fh:
+            fh.write(doc["inputs"].get(rel, ""))
+    return dest
+
+
+def replay(doc: dict, argv: Sequence[str] = None, extra_env: Optional[Dict[str, str]] = None
+           ) -> Tuple[Observation, Observation]:
+    """Returns (expected, got)."""
+    scenario = Scenario.from_json(doc["scenario"])
+    expected = Observation.from_json(doc["expected"])
+    tmp = tempfile.mkdtemp(prefix="tk8s-skel-")
+    try:
+        skel = build_skeleton(doc, os.path.join(tmp, "skel"))
+        with Sandbox(skel, scenario) as sbx:
+            got = sbx.run(list(argv or REPLACEMENT_ARGV), extra_env if extra_env is not None else REPLACEMENT_ENV)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return expected, got

@@ -272,11 +272,15 @@ class Supervisor:
     # ------------------------------------------------------------------
     # a3  getArgument  (setup.sh:94-110)
     # ------------------------------------------------------------------
-    def get_argument(self, message: str, default: str) -> str:
+    def get_argument(self, message: str, default: str, lineno: int = 0) -> str:
         """``$(getArgument "message" "default")``: empty answer (or EOF) = default.
-        Both branches ``echo`` unquoted."""
+        Both branches ``echo`` unquoted.  ``lineno`` is the reference line of the
+        call, which bash names when it drops a NUL byte from the substitution."""
         answer, _ok = self.rt.read("%s (%s) " % (message, default))
-        return self.echo_var(default if answer == "" else answer)
+        printed = sh.echo_unquoted(default if answer == "" else answer, self.rt.root)
+        if "\x00" in printed:
+            self.rt.err("%s: line %d: warning: command substitution: ignored null byte in input\n" % (self.program, lineno))
+        return sh.cmdsubst(printed)
 
     # ------------------------------------------------------------------
     # a4  getConfigFromUser  (setup.sh:255-451)
@@ -301,10 +305,11 @@ class Supervisor:
                 default_at = count
         return count, default_at
 
-    def _prompt_validated(self, message: str, var: str, ok: Callable[[str], bool], errors: List[str]) -> None:
+    def _prompt_validated(self, message: str, var: str, ok: Callable[[str], bool], errors: List[str],
+                          lineno: int) -> None:
         default = self.unq(self.v[var])  # evaluated once per attempt in the reference; it cannot change
         while True:
-            answer = self.get_argument(message, default)
+            answer = self.get_argument(message, default, lineno)
             if ok(answer):
                 self.v[var] = answer
                 return
@@ -317,34 +322,37 @@ class Supervisor:
         packages = self._menu_rows(TRITON_PACKAGES, kvm_only=True)
 
         self.echo(DASHES)
-        v["KUBERNETES_NAME"] = self.get_argument("Name your Kubernetes environment:", self.unq(v["KUBERNETES_NAME"]))
+        v["KUBERNETES_NAME"] = self.get_argument("Name your Kubernetes environment:", self.unq(v["KUBERNETES_NAME"]), 265)
         self.echo(DASHES)
         # the description default is whatever the description already holds
         # ("k8s dev" from the defaults), not the name just entered (setup.sh:267-271)
-        descr_default = v["KUBERNETES_NAME"] if v["KUBERNETES_DESCRIPTION"] == "" else v["KUBERNETES_DESCRIPTION"]
-        v["KUBERNETES_DESCRIPTION"] = self.get_argument("Describe this Kubernetes environment:", self.unq(descr_default))
+        blank = v["KUBERNETES_DESCRIPTION"] == ""
+        descr_default = v["KUBERNETES_NAME"] if blank else v["KUBERNETES_DESCRIPTION"]
+        v["KUBERNETES_DESCRIPTION"] = self.get_argument("Describe this Kubernetes environment:", self.unq(descr_default),
+                                                        268 if blank else 270)
         self.echo(DASHES)
         self._prompt_validated(
             "Hostname of the master:", "RANCHER_MASTER_HOSTNAME", lambda s: HOSTNAME_RE.fullmatch(s) is not None,
             ["error: Enter a valid hostname or leave blank to use the default.",
-             "    Must start with a letter and can only include letters and numbers"])
+             "    Must start with a letter and can only include letters and numbers"], 275)
         self.echo(DASHES)
         self._prompt_validated(
             "Enter a string to use for appending to hostnames of all the nodes:", "KUBERNETES_NODE_HOSTNAME_BEGINSWITH",
             lambda s: HOSTNAME_RE.fullmatch(s) is not None,
             ["error: Enter a valid value or leave blank to use the default.",
-             "    Must start with a letter and can only include letters and numbers"])
+             "    Must start with a letter and can only include letters and numbers"], 287)
         self.echo(DASHES)
         # hard limit 1-9: the setup has no HA (setup.sh:296)
         self._prompt_validated(
             "How many nodes should this Kubernetes cluster have:", "KUBERNETES_NUMBER_OF_NODES",
             lambda s: NODE_COUNT_RE.fullmatch(s) is not None,
-            ["error: Enter a valid value (number between 1-9) or leave blank to use the default."])
+            ["error: Enter a valid value (number between 1-9) or leave blank to use the default."], 300)
 
         public_at = 1
         for var, message, first in (
                 ("RANCHER_MASTER_NETWORKS", "What networks should the master be a part of, provide comma separated values:", True),
                 ("KUBERNETES_NODE_NETWORKS", "What networks should the nodes be a part of, provide comma separated values:", False)):
+            lineno = 332 if first else 375
             self.echo(DASHES)
             self.echo("From the networks below:")
             count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None)
@@ -352,7 +360,7 @@ class Supervisor:
                 public_at = at
             if v[var] == "":
                 v[var] = self.network_ids(self.args_of(str(public_at)))
-            self._prompt_index_list(var, message, count)
+            self._prompt_index_list(var, message, count, lineno)
 
         self.echo(DASHES)
         self.echo("From the packages below:")
@@ -377,12 +385,12 @@ class Supervisor:
                 bad += 1
         return bad
 
-    def _prompt_index_list(self, var: str, message: str, count: int) -> None:
+    def _prompt_index_list(self, var: str, message: str, count: int, lineno: int) -> None:
         v = self.v
         errors = ["error: Enter a valid option or leave blank to use the default.",
                   "    Values should be comma separated between 1 and %d." % count]
         while True:
-            answer = self.get_argument(message, self.unq(v[var]))
+            answer = self.get_argument(message, self.unq(v[var]), lineno)
             v[var] = self._normalise_list(v[var])
             answer = self._normalise_list(answer)
             shown = sh.echo_unquoted(answer, self.rt.root)
@@ -406,7 +414,7 @@ class Supervisor:
         errors = ["error: Enter a valid option or leave blank to use the default.",
                   "    Value should be between 1 and %d." % count]
         while True:
-            answer = self.get_argument("What KVM package should the master and nodes run on:", self.unq(v["HOST_PACKAGE"]))
+            answer = self.get_argument("What KVM package should the master and nodes run on:", self.unq(v["HOST_PACKAGE"]), 425)
             shown = sh.echo_unquoted(answer, self.rt.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_RE)) != "":
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
@@ -457,7 +465,7 @@ class Supervisor:
                 return rows
             self.rt.err("sed: -e expression #1, char %d: unknown command\n" % len(index))
             return ""
-        return tx.sed_print_line(rows, int(index))
+        return tx.sed_print_line(rows, int(index) & 0xFFFFFFFFFFFFFFFF)  # GNU sed line numbers wrap at 2**64
 
     # ------------------------------------------------------------------
     # a7  verifyConfig  (setup.sh:452-483)
@@ -509,6 +517,7 @@ class Supervisor:
         their literal double quotes from here on, and each line
         goes through ``read`` once more (backslashes processed again)."""
         text = tx.grep(self.rt.read_text("config"), r"^$", invert=True)
+        self.rt.write_text("config.tmp", text)  # stays behind if an export fails (errexit)
         data = sh.to_bytes(text)
         pos = 0
 
@@ -524,6 +533,7 @@ class Supervisor:
             if not ok:
                 break
             self._export(line)
+        os.remove(self.rt.path("config.tmp"))
 
     def _export(self, word: str) -> None:
         name, eq, value = word.partition("=")
@@ -646,7 +656,8 @@ class Supervisor:
                                        shown_src="ansible.cfg")
         self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml")
 
-    def _rewrite_private_key_file(self, cfg: str, tmp: str, delim: str, value: str, shown_src: str) -> None:
+    def _rewrite_private_key_file(self, cfg: str, tmp: str, delim: str, value: str, shown_src: str,
+                                  lineno: int = 133) -> None:
         """``sed "s<d>private_key_file = .*$<d>private_key_file = VALUE<d>g" cfg > tmp && mv tmp cfg``
         (setup.sh:133 with ';', setup.sh:511 with '~').  VALUE is spliced into the sed
         program text, so sed's own replacement syntax applies to it."""
@@ -655,7 +666,7 @@ class Supervisor:
         try:
             rt.write_text(tmp, "")  # the redirection creates/truncates the target first
         except OSError as exc:
-            rt.err("%s: %s: %s\n" % (self.program, tmp, exc.strerror))
+            rt.err("%s: line %d: %s: %s\n" % (self.program, lineno, os.path.basename(tmp), exc.strerror))
             return
         if repl is None:
             rt.err("sed: -e expression #1, char %d: unknown option to `s'\n" % (len(value) + 40))
@@ -781,7 +792,7 @@ class Supervisor:
         for pattern in ("terraform/terraform.*", "terraform/.terraform*"):
             for rel in sh.glob_word(pattern, rt.root):
                 _rm_rf(rt.path(rel))
-        self._rewrite_private_key_file("ansible/ansible.cfg", "tmp", "~", "", shown_src="ansible/ansible.cfg")
+        self._rewrite_private_key_file("ansible/ansible.cfg", "tmp", "~", "", shown_src="ansible/ansible.cfg", lineno=511)
         for rel in ["ansible/hosts", "ansible/ansible.cfg.tmp"] + sh.glob_word("ansible/*retry", rt.root):
             p = rt.path(rel)
             if os.path.isfile(p) or os.path.islink(p):
