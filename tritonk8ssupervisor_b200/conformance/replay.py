@@ -63,3 +63,19 @@ def replay(doc: dict, argv: Sequence[str] = None, extra_env: Optional[Dict[str, 
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
     return expected, got
+
+
+def replay_in_process(doc: dict) -> Tuple[Observation, Observation]:
+    """Like :func:`replay`, but the replacement runs in this process against the
+    in-memory tool models (no fork/exec).  Returns (expected, got)."""
+    from .modeltools import ModelSandbox
+    scenario = Scenario.from_json(doc["scenario"])
+    expected = Observation.from_json(doc["expected"])
+    tmp = tempfile.mkdtemp(prefix="tk8s-skel-")
+    try:
+        skel = build_skeleton(doc, os.path.join(tmp, "skel"))
+        with ModelSandbox(skel, scenario) as sbx:
+            got = sbx.run()
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return expected, got
