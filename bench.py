@@ -1,0 +1,267 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric for cheapRoc/tritonK8ssupervisor.
+
+    metric: offline validate/syntax-check pass rate per config   (unit: fraction of 5)
+
+THERE IS NO GPU WORK IN THIS BENCHMARK, and none in this repository.
+BASELINE.json flags the reference "TIER MISMATCH, no GPU graft target": it is
+551 lines of bash generating < 3.5 KB of text per run.  The
+line printed here therefore says ``"gpu_launches": 0`` and ``"roofline":
+{"bound": "n/a", ...}`` -- a roofline fraction for this path would be a made-up
+number -- and reports what *is* measurable:
+
+  value         pass rate over the five configs with the path run in-process
+                against in-memory tool models (inputs resident in memory: no
+                fork/exec, no pipes), + structural checks
+  e2e           the same pass rate through the public CLI
+                (``python -m tritonk8ssupervisor_b200``) as a child process in the
+                offline sandbox, talking to stub tool processes over pipes/files
+  cpu_baseline  the unmodified reference ``setup.sh`` under bash in the same
+                sandbox (kind "reference"), 1 core -- the script is sequential
+
+A "step" is one pass over the five configs.  Speed is secondary (SURVEY.md §8d:
+"Speed is not the metric"); it is reported as ms per step and configs/s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import time
+from typing import Any, Dict, List, Optional
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+os.environ.setdefault("LC_ALL", "C")
+
+from tritonk8ssupervisor_b200.conformance import harness, replay as rp  # noqa: E402
+from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS  # noqa: E402
+from tritonk8ssupervisor_b200.conformance.modeltools import ModelSandbox  # noqa: E402
+from tritonk8ssupervisor_b200.conformance.sandbox import Observation, Sandbox  # noqa: E402
+from tritonk8ssupervisor_b200.conformance.scenario import Scenario  # noqa: E402
+
+METRIC = "offline validate/syntax-check pass rate per config"
+UNIT = "fraction of the 5 BASELINE configs passing"
+WORKLOAD = "5 BASELINE.json configs (1, 2, 3, 5, 10->9 workers); one step = one pass over all five"
+NOT_APPLICABLE = ("not applicable: the path is a control path (bash integer counters, <= 3.5 KB of text written per "
+                  "config, 0 flops); BASELINE.json: 'TIER MISMATCH, no GPU graft target' (SURVEY.md §0, §8d)")
+
+
+# ---------------------------------------------------------------------------
+# the three ways of running one pass
+# ---------------------------------------------------------------------------
+def step_in_process(docs: List[dict]) -> List[harness.ConfigResult]:
+    """Resident leg: path in this process against in-memory tool models."""
+    out = []
+    for doc in docs:
+        sc = Scenario.from_json(doc["scenario"])
+        expected = Observation.from_json(doc["expected"])
+        res = harness.ConfigResult(name=sc.name)
+        t0 = time.perf_counter()
+        with ModelSandbox(harness.WORKSPACE_TEMPLATE, sc, input_overrides=doc["inputs"]) as sbx:
+            obs = sbx.run()
+            diffs = expected.diff(obs)
+            res.parity = not diffs
+            res.details += ["parity: %s" % d for d in diffs]
+            harness.check_generated_tree(sbx.workspace, obs, res)
+        res.deterministic = True  # checked by the e2e leg (two CLI runs per config)
+        res.wall_s = time.perf_counter() - t0
+        out.append(res)
+    return out
+
+
+def step_cli(docs: List[dict], repeat: int) -> List[harness.ConfigResult]:
+    """End-to-end leg: the public CLI as a child process in the sandbox."""
+    return [harness.run_config(doc, repeat=repeat) for doc in docs]
+
+
+def step_reference(docs: List[dict], ref_root: str) -> List[harness.ConfigResult]:
+    """Baseline leg: the unmodified reference under bash in the same sandbox; its
+    output is held to the goldens and to the same structural checks (run on the
+    reference's own terraform/ansible trees)."""
+    from oracle.reference_runner import REFERENCE_ARGV
+    out = []
+    for doc in docs:
+        sc = Scenario.from_json(doc["scenario"])
+        expected = Observation.from_json(doc["expected"])
+        res = harness.ConfigResult(name=sc.name)
+        t0 = time.perf_counter()
+        with Sandbox(ref_root, sc) as sbx:
+            obs = sbx.run(REFERENCE_ARGV)
+            diffs = expected.diff(obs)
+            res.parity = not diffs
+            res.details += ["parity: %s" % d for d in diffs]
+            harness.check_generated_tree(sbx.workspace, obs, res)
+        res.deterministic = True
+        res.wall_s = time.perf_counter() - t0
+        out.append(res)
+    return out
+
+
+def timed(fn, steps: int, warmup: int):
+    """(results of the last step, [seconds per timed step])."""
+    results = None
+    for _ in range(warmup):
+        results = fn()
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        results = fn()
+        times.append(time.perf_counter() - t0)
+    return results, times
+
+
+def sample_clocks() -> Optional[Dict[str, Any]]:
+    """GPU clocks are irrelevant to this benchmark; sampled once when
+    nvidia-smi exists so the line has the key the driver looks for."""
+    exe = shutil.which("nvidia-smi")
+    if not exe:
+        return None
+    try:
+        out = subprocess.run([exe, "--query-gpu=clocks.sm,clocks.max.sm,clocks_throttle_reasons.active",
+                              "--format=csv,noheader,nounits", "-i", "0"], capture_output=True, text=True, timeout=20).stdout
+        sm, mx, reasons = [x.strip() for x in out.strip().split(",")[:3]]
+        return {"sm_mhz": float(sm), "sm_max_mhz": float(mx), "reasons": [reasons],
+                "note": "GPU idle by design: this benchmark launches no kernels"}
+    except Exception as exc:  # pragma: no cover - diagnostics only
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "nvidia-smi failed: %s" % exc}
+
+
+# ---------------------------------------------------------------------------
+# multi-process plumbing: the path does not use GPUs and does not shard
+# (SURVEY.md §8e), so N ranks are N independent CPU replicas of the same pass
+# ---------------------------------------------------------------------------
+class Ranks:
+    def __init__(self) -> None:
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.dist = None
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            import torch.distributed as dist  # gloo: there is nothing on the device to reduce
+            dist.init_process_group(backend="gloo", rank=self.rank, world_size=self.world)
+            self.dist = dist
+
+    def barrier(self) -> None:
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def reduce(self, value: float, op: str) -> float:
+        if self.dist is None:
+            return value
+        import torch
+        t = torch.tensor([value], dtype=torch.float64)
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return float(t.item())
+
+    def close(self) -> None:
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def summarise(results: List[harness.ConfigResult]) -> Dict[str, Any]:
+    return {r.name: {"passed": r.passed, "parity": r.parity, "terraform": r.terraform, "ansible": r.ansible,
+                     "inventory": r.inventory, "deterministic": r.deterministic, "modules": r.n_modules,
+                     "hosts": r.n_hosts, "details": r.details[:3]} for r in results}
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--gpus", type=int, default=1, help="number of ranks (CPU replicas; no GPU is used)")
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    args = ap.parse_args(argv)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    docs = [harness.golden_for(sc) for sc in CONFIGS]
+    ranks = Ranks()
+
+    from oracle.reference_runner import find_reference  # the baseline legs are the only users of oracle/
+    ref_root = find_reference()
+
+    base = {"metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bytes (ASCII text)",
+            "data": "synthetic: fixture triton tables from the reference's walkthrough (docs/detailed.md:156-195), "
+                    "stub tools, fixed answers", "gpu_launches": 0,
+            "config": {"workload": WORKLOAD, "l2_policy": "n/a (no device buffers)",
+                       "parallelism": "%d independent CPU replica(s); the path does not shard (SURVEY.md §8e)" % ranks.world},
+            "roofline": {"bound": "n/a", "achieved": None, "peak": None, "unit": None, "frac": None, "traffic": None,
+                         "note": NOT_APPLICABLE}}
+
+    if args.impl == "reference":
+        if ranks.rank != 0:
+            ranks.close()
+            return 0
+        if ref_root is None:
+            print(json.dumps({"impl": "reference", "unavailable": "no reference tree: neither /root/reference nor the staged oracle/_ref/reference"}))
+            return 0
+        results, times = timed(lambda: step_reference(docs, ref_root), steps, warmup)
+        ms = 1e3 * statistics.mean(times)
+        rate = harness.pass_rate(results)
+        line = dict(base, impl="reference", value=rate, ms_per_step=ms, configs_per_s=len(docs) / (ms / 1e3),
+                    clocks=sample_clocks(), per_config=summarise(results),
+                    cpu_baseline={"value": rate, "unit": UNIT, "cores": 1, "kind": "reference",
+                                  "sample": "all 5 configs x %d steps, unmodified setup.sh under bash in the stub sandbox (%s)" % (steps, ref_root),
+                                  "ms_per_step": ms},
+                    e2e={"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+        print(json.dumps(line))
+        ranks.close()
+        return 0
+
+    # -- our arm -------------------------------------------------------------
+    for _ in range(warmup):
+        step_in_process(docs)
+    ranks.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        results = step_in_process(docs)
+    local = time.perf_counter() - t0
+    ranks.barrier()
+    total = ranks.reduce(local, "MAX")            # max over ranks
+    rate = ranks.reduce(harness.pass_rate(results), "MIN")
+    ms = 1e3 * total / steps
+
+    # end to end through the CLI: 2 runs per config (the second proves determinism)
+    e2e_results, e2e_times = timed(lambda: step_cli(docs, repeat=2), max(1, min(steps, 3)), 1)
+    e2e_rate = ranks.reduce(harness.pass_rate(e2e_results), "MIN")
+    e2e_ms = 1e3 * ranks.reduce(statistics.mean(e2e_times), "MAX")
+    stdin_bytes = sum(len(d["scenario"]["stdin"]) for d in docs)
+    out_bytes = sum(len(c) for d in docs for c in d["expected"]["files"].values()) + sum(len(d["expected"]["stdout"]) for d in docs)
+
+    cpu_baseline: Dict[str, Any]
+    if ranks.rank == 0 and args.gpus == 1 and ref_root is not None:
+        ref_results, ref_times = timed(lambda: step_reference(docs, ref_root), 3, 1)
+        ref_ms = 1e3 * statistics.mean(ref_times)
+        cpu_baseline = {"value": harness.pass_rate(ref_results), "unit": UNIT, "cores": 1, "kind": "reference",
+                        "sample": "all 5 configs x 3 steps, unmodified setup.sh under bash in the stub sandbox",
+                        "ms_per_step": ref_ms, "configs_per_s": len(docs) / (ref_ms / 1e3)}
+    else:
+        cpu_baseline = {"value": None, "unit": UNIT, "cores": 1, "kind": "reference",
+                        "sample": "not run (rank != 0, N > 1, or no reference tree on this machine)"}
+
+    extension = harness.extension_count_scaling(10) if ranks.rank == 0 else None
+    if ranks.rank == 0:
+        line = dict(base, value=rate, ms_per_step=ms, configs_per_s=ranks.world * len(docs) / (ms / 1e3),
+                    clocks=sample_clocks(), per_config=summarise(e2e_results),
+                    e2e={"value": e2e_rate, "unit": UNIT, "ms_per_step": e2e_ms,
+                         "configs_per_s": ranks.world * len(docs) / (e2e_ms / 1e3),
+                         "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                         "stdin_bytes_per_step": stdin_bytes, "output_bytes_per_step": out_bytes,
+                         "note": "public CLI as a child process, stub tools as child processes; 2 runs per config; no device"},
+                    cpu_baseline=cpu_baseline,
+                    extension_config5b={k: extension[k] for k in ("ok", "n_workers", "modules", "planned_machines",
+                                                                   "inventory_hosts", "rancher_tf_bytes", "size_law")})
+        print(json.dumps(line))
+    ranks.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,106 @@
+"""The five-config harness (BASELINE.json's metric) and its failure modes."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from tritonk8ssupervisor_b200.conformance import harness
+from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_five_of_five():
+    results = harness.run_all()
+    assert [r.name for r in results] == [c.name for c in CONFIGS]
+    for r in results:
+        assert r.passed, (r.name, r.details)
+    assert harness.pass_rate(results) == 1.0
+    assert [r.n_modules for r in results] == [2, 3, 4, 6, 10]      # 1 master + N workers
+    assert [r.n_hosts for r in results] == [2, 3, 4, 6, 10]
+
+
+@pytest.mark.gpu
+def test_five_of_five_on_box():
+    """Selected by ``-m gpu``; no GPU is used (see conftest)."""
+    assert harness.pass_rate(harness.run_all()) == 1.0
+
+
+def test_count_scaling_extension():
+    ext = harness.extension_count_scaling(10)
+    assert ext["ok"], ext
+    assert ext["modules"] == 11 and ext["planned_machines"] == 11 and ext["inventory_hosts"] == 11
+    assert ext["size_law"]["per_worker"] == 234          # +234 bytes per worker block
+
+
+def test_a_wrong_implementation_fails_parity(tmp_path):
+    """The harness must be able to say no: an implementation that gets one byte
+    wrong scores 0 on parity."""
+    bad = tmp_path / "bad.py"
+    bad.write_text(
+        "import sys, runpy\n"
+        "import tritonk8ssupervisor_b200.supervisor as s\n"
+        "s.DASHES = '--------------'\n"                       # one dash short
+        "sys.argv = ['setup.sh'] + sys.argv[1:]\n"
+        "runpy.run_module('tritonk8ssupervisor_b200', run_name='__main__')\n")
+    res = harness.run_config(harness.golden_for(CONFIGS[0]), argv=[sys.executable, str(bad)], repeat=1)
+    assert not res.parity and not res.passed
+    assert res.terraform and res.ansible and res.inventory
+
+
+def test_structural_failure_is_detected(tmp_path):
+    """Break a module of the workspace: parity still holds, terraform check fails."""
+    import shutil
+    ws = tmp_path / "ws"
+    shutil.copytree(harness.WORKSPACE_TEMPLATE, ws)
+    p = ws / "terraform" / "host" / "inputs.tf"
+    p.write_text(p.read_text().replace('variable "package"', 'variable "packge"'))
+    res = harness.run_config(harness.golden_for(CONFIGS[1]), workspace_src=str(ws), repeat=1)
+    assert res.parity and not res.terraform and not res.passed
+    assert any("arg-unknown" in d for d in res.details)
+
+
+def test_bench_line_contract():
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert p.returncode == 0, p.stderr
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks"):
+        assert key in d, key
+    assert d["value"] == 1.0 and d["e2e"]["value"] == 1.0
+    assert d["gpu_launches"] == 0 and d["roofline"]["frac"] is None and d["vs_baseline"] is None
+    assert "workload" in d["config"]
+
+
+def test_bench_reference_arm(ref_root):
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert p.returncode == 0, p.stderr
+    d = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][0])
+    assert d["impl"] == "reference" and d["value"] == 1.0 and d["cpu_baseline"]["kind"] == "reference"
+    assert d["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_bench_two_ranks_gloo():
+    """N > 1: independent CPU replicas, gloo for the barrier and the max/min over
+    ranks; rank 0 prints the one line."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["n_gpus"] == 2 and d["value"] == 1.0 and d["e2e"]["value"] == 1.0
+    assert d["cpu_baseline"]["value"] is None      # baseline is timed at N=1 only
