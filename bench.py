@@ -228,8 +228,12 @@ def main(argv=None) -> int:
     rate = ranks.reduce(harness.pass_rate(results), "MIN")
     ms = 1e3 * total / steps
 
-    # end to end through the CLI: 2 runs per config (the second proves determinism)
-    e2e_results, e2e_times = timed(lambda: step_cli(docs, repeat=2), max(1, min(steps, 3)), 1)
+    # end to end through the CLI: one run per config is timed (comparable with the
+    # reference arm); a second, untimed pass of two runs per config proves determinism
+    e2e_results, e2e_times = timed(lambda: step_cli(docs, repeat=1), max(1, min(steps, 3)), 1)
+    det_results = step_cli(docs, repeat=2)
+    for r, d in zip(e2e_results, det_results):
+        r.deterministic = d.deterministic and d.parity
     e2e_rate = ranks.reduce(harness.pass_rate(e2e_results), "MIN")
     e2e_ms = 1e3 * ranks.reduce(statistics.mean(e2e_times), "MAX")
     stdin_bytes = sum(len(d["scenario"]["stdin"]) for d in docs)
@@ -254,7 +258,7 @@ def main(argv=None) -> int:
                          "configs_per_s": ranks.world * len(docs) / (e2e_ms / 1e3),
                          "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                          "stdin_bytes_per_step": stdin_bytes, "output_bytes_per_step": out_bytes,
-                         "note": "public CLI as a child process, stub tools as child processes; 2 runs per config; no device"},
+                         "note": "public CLI as a child process, stub tools as child processes; 1 timed run per config (+ an untimed second pass for determinism); no device"},
                     cpu_baseline=cpu_baseline,
                     extension_config5b={k: extension[k] for k in ("ok", "n_workers", "modules", "planned_machines",
                                                                    "inventory_hosts", "rancher_tf_bytes", "size_law")})
