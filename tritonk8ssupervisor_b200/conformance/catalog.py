@@ -219,3 +219,17 @@ EDGE: List[Scenario] = [
 ALL: List[Scenario] = CONFIGS + EDGE
 BY_NAME: Dict[str, Scenario] = {s.name: s for s in ALL}
 assert len(BY_NAME) == len(ALL), "duplicate scenario names"
+
+# ---------------------------------------------------------------------------
+# interactive cases: (scenario, answers typed at the terminal one prompt at a time)
+# ---------------------------------------------------------------------------
+TTY_CASES = [
+    (Scenario(name="tty_quickstart", note="README.md:112-121: every prompt with its default, '2' typed at the node count"),
+     ["", "", "", "", "2", "", "", "", "yes"]),
+    (Scenario(name="tty_reprompts", note="invalid answers: error lines, then the same prompt again"),
+     ["my env", "", "1bad", "km1", "w", "wk", "0", "3", "9", "2,4", "x", "1", "99", "10", "maybe", "yes"]),
+    (Scenario(name="tty_decline", note="'no' at the confirmation"), ["", "", "", "", "", "", "", "", "no"]),
+    (Scenario(name="tty_clean", args=["-c"], pre_files={"terraform/masters.ip": "10.0.0.1\n", "terraform/hosts.ip": "10.0.1.1\n"},
+              note="clean prompt wording when machines exist (setup.sh:487-493)"), ["what", "yes"]),
+    (Scenario(name="tty_clean_fresh", args=["-c"], note="clean prompt wording on a fresh tree (setup.sh:495)"), ["no"]),
+]
