@@ -104,3 +104,23 @@ def test_bench_two_ranks_gloo():
     d = json.loads(lines[0])
     assert d["n_gpus"] == 2 and d["value"] == 1.0 and d["e2e"]["value"] == 1.0
     assert d["cpu_baseline"]["value"] is None      # baseline is timed at N=1 only
+
+
+def test_triton_table_cache_changes_only_the_trace():
+    """TK8S_CACHE_TRITON=1: byte-identical stdout and files, strictly fewer
+    `triton` calls (one `networks`, one `packages`), nothing else reordered."""
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    from tritonk8ssupervisor_b200.conformance.sandbox import Observation
+    for sc in CONFIGS:
+        doc = harness.golden_for(sc)
+        env = dict(rp.REPLACEMENT_ENV, TK8S_CACHE_TRITON="1")
+        want, got = rp.replay(doc, extra_env=env)
+        assert (got.stdout, got.stderr, got.exit_status, got.removed) == (want.stdout, want.stderr, want.exit_status, want.removed)
+        assert got.files == want.files
+
+        def strip(calls):
+            return [c for c in calls if not c.startswith("triton|") and "TK8S_CACHE_TRITON" not in c]
+        assert strip(got.calls) == strip(want.calls)
+        triton = [c for c in got.calls if c.startswith("triton|")]
+        assert triton == ["triton|.|env", "triton|.|networks -oname,id", "triton|.|packages -oname,id"]
+        assert len([c for c in want.calls if c.startswith("triton|")]) >= 6      # env + 2 menus + 3 default resolutions

@@ -9,6 +9,8 @@ Environment:
   TK8S_EXTERNAL_CLOCK=1  take ``sleep``/``date +%s`` from PATH (as the reference
                          does) instead of in-process calls; used by the offline
                          harness to script time.
+  TK8S_CACHE_TRITON=1    fetch each `triton` table once instead of once per
+                         resolved index (same files, fewer CloudAPI round trips).
 """
 from __future__ import annotations
 

@@ -35,7 +35,6 @@ Function-by-function correspondence (reference file:line):
 """
 from __future__ import annotations
 
-import glob as _glob
 import os
 import re
 import shutil
@@ -89,6 +88,8 @@ class Supervisor:
         self.program = program
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
+        self.cache_triton = rt.env.get("TK8S_CACHE_TRITON", "") == "1"
+        self._tables: Dict[tuple, str] = {}
 
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
@@ -288,11 +289,24 @@ class Supervisor:
     def _menu_rows(self, argv: List[str], kvm_only: bool) -> str:
         """The table a menu is built from: header dropped, runs of blanks
         squeezed, blanks turned into '=', sorted (setup.sh:257,259)."""
-        _, text = self.rt.run(argv, stdout=CAPTURE)
+        text = self._triton_table(argv)
         if kvm_only:
             text = tx.grep(text, r"-kvm-")
         text = tx.grep(text, r"^NAME.*ID$", invert=True)
         return sh.cmdsubst(tx.sort_lines(tx.tr(tx.tr_squeeze_spaces(text), " ", "=")))
+
+    def _triton_table(self, argv: List[str]) -> str:
+        """Output of ``triton networks|packages -oname,id``.  The reference asks the
+        CLI again for every index it resolves (3 + k ``networks`` and 2-3
+        ``packages`` calls per run, each a CloudAPI round trip); with
+        ``TK8S_CACHE_TRITON=1`` each table is fetched once.  Off by default: it
+        shortens the child-process trace, which the parity tests compare."""
+        key = tuple(argv)
+        if self.cache_triton and key in self._tables:
+            return self._tables[key]
+        _, text = self.rt.run(argv, stdout=CAPTURE)
+        self._tables[key] = text
+        return text
 
     def _print_menu(self, rows: str, default_prefix: Optional[str]) -> Tuple[int, int]:
         """Numbered menu; returns (row count, 1-based position of the default row)."""
@@ -443,7 +457,7 @@ class Supervisor:
         values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
         acc = ""
         for index in self.args_of(values):
-            _, text = self.rt.run(TRITON_NETWORKS, stdout=CAPTURE)
+            text = self._triton_table(TRITON_NETWORKS)
             rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
             acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
@@ -451,7 +465,7 @@ class Supervisor:
 
     def package_id(self, args: List[str]) -> str:
         arg1 = args[0] if args else ""
-        _, text = self.rt.run(TRITON_PACKAGES, stdout=CAPTURE)
+        text = self._triton_table(TRITON_PACKAGES)
         rows = tx.grep(tx.grep(text, r"-kvm-"), r"^NAME.*ID$", invert=True)
         rows = tx.sort_lines(tx.tr_squeeze_spaces(rows))
         picked = sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)))
