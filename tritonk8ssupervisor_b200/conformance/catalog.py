@@ -179,6 +179,17 @@ EDGE: List[Scenario] = [
              note="banner URLs come from masters.ip and the id the playbook stored"),
     Scenario(name="env_id_missing", stdin=BLANK8 + YES, pre_remove=["ansible/tmp/kubernetes_environment.id"],
              note="no stored id: cat fails inside $(...), URLs have an empty id"),
+    # --- tools that are not installed (bash: "command not found", status 127) ---
+    Scenario(name="missing_triton", stdin="yes\n", missing_tools=["triton"],
+             note="no triton CLI: eval of nothing, empty SDC_*, menus empty; the first ssh file 'matches' the empty id"),
+    Scenario(name="missing_ssh_keygen", stdin="yes\n", missing_tools=["ssh-keygen"],
+             note="no ssh-keygen: messages hidden by 2>/dev/null, key never found, clean, exit 1"),
+    Scenario(name="missing_terraform", stdin=BLANK8 + YES, missing_tools=["terraform"],
+             note="no terraform: rancher.tf is written, then errexit with 127"),
+    Scenario(name="missing_ansible", stdin=BLANK8 + YES, missing_tools=["ansible-playbook"],
+             note="no ansible-playbook: machines exist, inventory written, errexit with 127"),
+    Scenario(name="missing_terraform_on_clean", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES, missing_tools=["terraform"],
+             note="clean without terraform: the failed destroy is swallowed, files are removed anyway"),
     # --- dashboard wait loop (setup.sh:59-85) ---------------------------------
     Scenario(name="wait_not_on_15s_boundary", stdin=BLANK8 + YES, date_seq=["1500000001", "1500000002", "1500000014"],
              note="curl is only tried when epoch % 15 == 0"),

@@ -66,8 +66,15 @@ class ModelRuntime(Runtime):
 
     # -- tools -------------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT) -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
         tool, args = argv[0], list(argv[1:])
+        if tool in self.sc.missing_tools:
+            msg = "%s%s: command not found\n" % (where + ": " if where else "", tool)
+            if stderr == INHERIT:
+                self.stderr.append(msg)
+            elif stderr == TO_STDOUT:
+                self.stdout.append(msg)
+            return 127, ""
         rel = "." if cwd in (".", "") else "./" + cwd
         self.calls.append("%s|%s|%s" % (tool, rel, " ".join(args)))
         if tool in ("terraform", "ansible-playbook"):

@@ -128,6 +128,8 @@ class Scenario:
     ssh_exit: Dict[str, int] = dataclasses.field(default_factory=dict)
     #: ``$HOME/.ssh/known_hosts`` present (setup.sh:504)
     known_hosts: Optional[str] = None
+    #: tools that are not installed at all (no stub on PATH): bash says "command not found"
+    missing_tools: List[str] = dataclasses.field(default_factory=list)
     note: str = ""
 
     def to_json(self) -> dict:

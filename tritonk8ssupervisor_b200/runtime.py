@@ -54,8 +54,10 @@ class Runtime:
 
     # -- children ----------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT) -> Tuple[int, str]:
-        """Run a tool; returns (exit status, captured stdout or '')."""
+            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
+        """Run a tool; returns (exit status, captured stdout or '').  ``where``
+        ("setup.sh: line 157") prefixes the shell's own diagnostics, e.g. when
+        the tool is not installed."""
         raise NotImplementedError
 
     def sleep(self, seconds: int) -> int:
@@ -131,7 +133,7 @@ class HostRuntime(Runtime):
         return bashsem.read_builtin(self._next_byte)
 
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT) -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
         out_target = {INHERIT: self.stdout_fd, DEVNULL: subprocess.DEVNULL,
                       CAPTURE: subprocess.PIPE}[stdout]
         err_target = {INHERIT: self.stderr_fd, DEVNULL: subprocess.DEVNULL,
@@ -139,14 +141,16 @@ class HostRuntime(Runtime):
         try:
             proc = subprocess.Popen(list(argv), cwd=self.path(cwd), env=self.env,
                                     stdin=self.stdin_fd, stdout=out_target, stderr=err_target)
-        except FileNotFoundError:
+        except (FileNotFoundError, PermissionError) as exc:
+            # what bash says; the message follows the command's own redirections
+            missing = isinstance(exc, FileNotFoundError)
+            msg = "%s%s: %s\n" % (where + ": " if where else "", argv[0],
+                                  "command not found" if missing else "Permission denied")
             if stderr == INHERIT:
-                self.err("%s: command not found\n" % argv[0])
-            return 127, ""
-        except PermissionError:
-            if stderr == INHERIT:
-                self.err("%s: Permission denied\n" % argv[0])
-            return 126, ""
+                self.err(msg)
+            elif stderr == TO_STDOUT:
+                self.out(msg)
+            return (127 if missing else 126), ""
         data, _ = proc.communicate()
         status = proc.returncode
         if status < 0:

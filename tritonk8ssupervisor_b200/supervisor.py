@@ -129,6 +129,10 @@ class Supervisor:
             self.rt.err("cat: %s: %s\n" % (rel, exc.strerror))
             return ""
 
+    def at(self, line: int) -> str:
+        """``setup.sh: line N`` -- how bash labels its own diagnostics."""
+        return "%s: line %d" % (self.program, line)
+
     def must(self, status: int) -> None:
         """errexit: an unguarded child failure is the script's exit status."""
         if status != 0:
@@ -222,7 +226,7 @@ class Supervisor:
     # ------------------------------------------------------------------
     def set_config_from_triton(self) -> None:
         rt, v = self.rt, self.v
-        _, text = rt.run(["triton", "env"], stdout=CAPTURE)  # status is swallowed by eval "$(...)"
+        _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210))  # status is swallowed by eval "$(...)"
         try:
             apply_triton_env(sh.cmdsubst(text), v, rt.env)
         except TritonEnvError as exc:
@@ -289,13 +293,13 @@ class Supervisor:
     def _menu_rows(self, argv: List[str], kvm_only: bool) -> str:
         """The table a menu is built from: header dropped, runs of blanks
         squeezed, blanks turned into '=', sorted (setup.sh:257,259)."""
-        text = self._triton_table(argv)
+        text = self._triton_table(argv, 259 if kvm_only else 257)
         if kvm_only:
             text = tx.grep(text, r"-kvm-")
         text = tx.grep(text, r"^NAME.*ID$", invert=True)
         return sh.cmdsubst(tx.sort_lines(tx.tr(tx.tr_squeeze_spaces(text), " ", "=")))
 
-    def _triton_table(self, argv: List[str]) -> str:
+    def _triton_table(self, argv: List[str], line: int) -> str:
         """Output of ``triton networks|packages -oname,id``.  The reference asks the
         CLI again for every index it resolves (3 + k ``networks`` and 2-3
         ``packages`` calls per run, each a CloudAPI round trip); with
@@ -304,7 +308,7 @@ class Supervisor:
         key = tuple(argv)
         if self.cache_triton and key in self._tables:
             return self._tables[key]
-        _, text = self.rt.run(argv, stdout=CAPTURE)
+        _, text = self.rt.run(argv, stdout=CAPTURE, where=self.at(line))
         self._tables[key] = text
         return text
 
@@ -457,7 +461,7 @@ class Supervisor:
         values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
         acc = ""
         for index in self.args_of(values):
-            text = self._triton_table(TRITON_NETWORKS)
+            text = self._triton_table(TRITON_NETWORKS, 536)
             rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
             acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
@@ -465,7 +469,7 @@ class Supervisor:
 
     def package_id(self, args: List[str]) -> str:
         arg1 = args[0] if args else ""
-        text = self._triton_table(TRITON_PACKAGES)
+        text = self._triton_table(TRITON_PACKAGES, 541)
         rows = tx.grep(tx.grep(text, r"-kvm-"), r"^NAME.*ID$", invert=True)
         rows = tx.sort_lines(tx.tr_squeeze_spaces(rows))
         picked = sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)))
@@ -583,8 +587,8 @@ class Supervisor:
             self.update_terraform_config(["host"] + self.args_of(self.unq("%s%d" % (prefix, i))))
             i += 1
         self.echo("Starting terraform tasks")
-        self.must(rt.run(["terraform", "get"], cwd="terraform")[0])
-        self.must(rt.run(["terraform", "apply"], cwd="terraform")[0])
+        self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156))[0])
+        self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157))[0])
         self.echo("    terraform tasks completed")
 
     def _arith(self, text: str) -> int:
@@ -700,7 +704,7 @@ class Supervisor:
         if not os.path.isdir(self.rt.path("ansible")):
             self.rt.err("%s: line 112: cd: ansible: No such file or directory\n" % self.program)
             raise ScriptExit(1)
-        self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible")[0])
+        self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible", where=self.at(113))[0])
 
     # ------------------------------------------------------------------
     # dashboard wait loop  (setup.sh:59-85)
@@ -713,13 +717,13 @@ class Supervisor:
             (":8080/r/projects/", False), (self.cat_subst("ansible/tmp/kubernetes_environment.id"), True),
             ("/kubernetes-dashboard:9090/", False)], self.rt.root)
 
-    def _curl_dashboard(self) -> Tuple[int, str]:
+    def _curl_dashboard(self, line: int) -> Tuple[int, str]:
         return self.rt.run(["curl", "--connect-timeout", "5", "--max-time", "5", "-s"] + self._dashboard_url_words(),
-                           stdout=CAPTURE)
+                           stdout=CAPTURE, where=self.at(line))
 
-    def _ssh_docker_ps(self, node: str) -> str:
+    def _ssh_docker_ps(self, node: str, line: int) -> str:
         return self.rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node, "docker", "ps"],
-                           stdout=CAPTURE)[1]
+                           stdout=CAPTURE, where=self.at(line))[1]
 
     def wait_for_dashboard(self) -> None:
         """Poll once a second; every time the epoch is a multiple of 15 ask the
@@ -735,7 +739,7 @@ class Supervisor:
             now = sh.cmdsubst(rt.epoch())
             if not re.fullmatch(r"[0-9]+", now) or int(now) % 15 != 0:
                 continue
-            status, body = self._curl_dashboard()
+            status, body = self._curl_dashboard(66)
             self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
             shown = sh.echo_unquoted(sh.cmdsubst(body), rt.root)
             if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True)) != 0:
@@ -743,15 +747,15 @@ class Supervisor:
                 continue
             count = 0
             for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
-                ps = tx.grep(self._ssh_docker_ps(node), r"kubernetes-dashboard")
+                ps = tx.grep(self._ssh_docker_ps(node, 70), r"kubernetes-dashboard")
                 count += tx.wc_w(tx.awk_print_field(ps, 1))
             if count != 2:
                 continue
-            _, body = self._curl_dashboard()
+            _, body = self._curl_dashboard(72)
             if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True)) == 0:
                 continue
             for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
-                ps = tx.grep(self._ssh_docker_ps(node), r"k8s_POD.*dashboard")
+                ps = tx.grep(self._ssh_docker_ps(node, 74), r"k8s_POD.*dashboard")
                 container = sh.cmdsubst(tx.awk_print_field(ps, 1))
                 if container != "":
                     status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,
@@ -799,7 +803,7 @@ class Supervisor:
             recorded = sh.cmdsubst(rt.read_text("terraform/hosts.ip") + rt.read_text("terraform/masters.ip"))
             for host_key in self.args_of(recorded):
                 # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped
-                status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT)
+                status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT, where=self.at(506))
                 self.must(status)
         for rel in ("terraform/hosts.ip", "terraform/masters.ip", "terraform/rancher.tf"):
             _rm_rf(rt.path(rel))
