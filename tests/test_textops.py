@@ -1,0 +1,67 @@
+"""textops restates grep/sed/tr/sort/uniq/awk/tail/wc for the option sets the
+path uses; here each is checked against the real tool (coreutils/sed/awk are in
+the image, LC_ALL=C)."""
+import subprocess
+
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from tritonk8ssupervisor_b200 import textops as tx
+from tritonk8ssupervisor_b200.bashsem import from_bytes, to_bytes
+
+ENV = {"PATH": "/usr/bin:/bin", "LC_ALL": "C"}
+
+
+def real(argv, text):
+    p = subprocess.run(argv, input=to_bytes(text), stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, env=ENV)
+    return from_bytes(p.stdout)
+
+
+_line = st.text(st.sampled_from(list("ab =,-kvmNAMEID01\t\"")), max_size=12)
+_text = st.builds(lambda ls, nl: "\n".join(ls) + ("\n" if nl and ls else ""), st.lists(_line, max_size=8), st.booleans())
+
+CASES = [
+    (lambda t: tx.sort_lines(t), ["sort"]),
+    (lambda t: tx.uniq(t), ["uniq"]),
+    (lambda t: tx.tr_squeeze_spaces(t), ["tr", "-s", " "]),
+    (lambda t: tx.tr(t, " ", "="), ["tr", " ", "="]),
+    (lambda t: tx.tr(t, ",", "\n"), ["tr", ",", "\n"]),
+    (lambda t: tx.tr(t, "\n", ","), ["tr", "\n", ","]),
+    (lambda t: tx.grep(t, r"-kvm-"), ["grep", r"\-kvm-"]),
+    (lambda t: tx.grep(t, r"^NAME.*ID$", invert=True), ["grep", "-v", "^NAME.*ID$"]),
+    (lambda t: tx.grep(t, r"^NAME *ID$", invert=True), ["grep", "-v", "^NAME *ID$"]),
+    (lambda t: tx.grep(t, r"^$", invert=True), ["grep", "-v", "^$"]),
+    (lambda t: tx.grep(t, r"name", ignore_case=True), ["grep", "-i", "name"]),
+    (lambda t: tx.grep(t, r"^[1-9][0-9]?(,[1-9][0-9]?)*$"), ["grep", r"^[1-9][0-9]\?\(,[1-9][0-9]\?\)*$"]),
+    (lambda t: tx.strip_dquotes(t), ["sed", 's/"//g']),
+    (lambda t: tx.sed_sub(t, r"=", "  ", count=0), ["sed", "s/=/  /g"]),
+    (lambda t: tx.sed_sub(t, r",", '","', count=0), ["sed", 's/,/","/g']),
+    (lambda t: tx.sed_sub(t, r"^(.*),$", r"\1"), ["sed", r"s/\(.*\),$/\1/"]),
+    (lambda t: tx.sed_sub(t, r"^,(.*)$", r"\1"), ["sed", r"s/^,\(.*\)$/\1/"]),
+    (lambda t: tx.sed_sub(t, r".pub$", ""), ["sed", "s/.pub$//"]),
+    (lambda t: tx.sed_print_line(t, 2), ["sed", "-n", "2p"]),
+    (lambda t: tx.sed_print_line(t, 9), ["sed", "-n", "9p"]),
+    (lambda t: tx.awk_print_field(t, 2), ["awk", "{print $2}"]),
+    (lambda t: tx.awk_print_field(t, 1), ["awk", "{print $1}"]),
+    (lambda t: tx.awk_last_field_if_many(t), ["awk", "NF>1{print $NF}"]),
+    (lambda t: tx.tail_1(t), ["tail", "-1"]),
+    (lambda t: "%d\n" % tx.wc_l(t), ["wc", "-l"]),
+    (lambda t: "%d\n" % tx.wc_w(t), ["wc", "-w"]),
+]
+
+FIXED = ["", "\n", "a\n", "a", "b\na\nb\n", "NAME   ID\nk4-kvm-1  u1\nx  u2\n", "2,4,\n", ",a,b\n", "a  b   c\n \n",
+         "id_rsa.pub\nmypub\n", "x\n\ny\n", "1,2\n10,2\n007\n", 'say "hi"\n', "\t lead\ttab  \n", "a\n\n"]
+
+
+@pytest.mark.parametrize("idx", range(len(CASES)), ids=[" ".join(c[1]) for c in CASES])
+def test_against_real_tool_fixed(idx):
+    ours, argv = CASES[idx]
+    for text in FIXED:
+        assert ours(text) == real(argv, text), (argv, text)
+
+
+@settings(max_examples=25, deadline=None, derandomize=True)
+@given(text=_text)
+def test_against_real_tools_random(text):
+    for ours, argv in CASES:
+        assert ours(text) == real(argv, text), (argv, text)

@@ -1,0 +1,79 @@
+"""`triton env` output is parsed, not eval-ed (deviation 1).  For
+the accepted dialect the parser must leave exactly the variables that bash's
+``eval`` leaves; everything else must be refused."""
+import subprocess
+
+import pytest
+
+from tritonk8ssupervisor_b200.conformance.scenario import triton_env_text
+from tritonk8ssupervisor_b200.tritonenv import TritonEnvError, apply_triton_env
+
+NAMES = ["SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID", "SDC_USER", "SDC_TESTING", "TRITON_PROFILE", "DOCKER_HOST", "PLAIN", "EMPTY"]
+START = {"SDC_USER": "old-user", "SDC_TESTING": "1", "PLAIN": "exported-before"}
+
+
+def bash_eval(text):
+    """(shell value, exported?) per name after `eval "$text"` in a real bash."""
+    script = 'eval "$1"; shift; for n in "$@"; do if [ -n "${!n+x}" ]; then printf "%s=%s|%s\\036" "$n" "${!n}" ' \
+             '"$(env | grep -c "^$n=")"; fi; done'
+    env = dict(START, PATH="/usr/bin:/bin", LC_ALL="C")
+    p = subprocess.run(["bash", "-c", script, "_", text] + NAMES, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
+    out = {}
+    for rec in p.stdout.decode().split("\x1e")[:-1]:
+        kv, _, exported = rec.rpartition("|")
+        k, _, v = kv.partition("=")
+        out[k] = (v, exported != "0")
+    return out
+
+
+def ours(text):
+    shell, env = dict(START), dict(START)
+    apply_triton_env(text, shell, env)
+    return {n: (shell[n], n in env) for n in NAMES if n in shell}
+
+
+ACCEPTED = [
+    triton_env_text(),
+    triton_env_text(url="https://eu-ams-1.api.joyent.com", account="acme corp", key_id="SHA256:abc/def+ghi="),
+    'export SDC_URL=https://bare.example\nexport SDC_ACCOUNT="q\\"uote"\n',
+    "export SDC_URL='single $HOME `x`'\n",
+    'export SDC_URL="a" SDC_ACCOUNT="b"; export SDC_KEY_ID=c\n',
+    "PLAIN=changed\nEMPTY=\nexport EMPTY\n",
+    "unset SDC_USER SDC_TESTING\n# comment\n\n   \n",
+    'export DOCKER_HOST=tcp://1.2.3.4:2376 # trailing comment\n',
+    'export SDC_URL="with#hash" SDC_ACCOUNT=a#b\n',
+    'export SDC_URL=back\\ slash\\"x\n',
+    "export SDC_ACCOUNT\n",
+    "",
+]
+
+
+@pytest.mark.parametrize("text", ACCEPTED, ids=range(len(ACCEPTED)))
+def test_same_variables_as_bash_eval(text):
+    assert ours(text) == bash_eval(text)
+
+
+@pytest.mark.parametrize("text", [
+    'export SDC_URL="$(curl evil)"\n', "export SDC_URL=`id`\n", 'export SDC_URL="$HOME/x"\n', "rm -rf /\n",
+    "export SDC_URL=a | tee x\n", "export 1BAD=x\n", "export SDC_URL=$HOME\n", "echo hi > /tmp/x\n", "export A=(1 2)\n",
+    'export SDC_URL="unterminated\n', "export SDC_URL='unterminated\n", "eval foo\n", "A=1 B=2\n",
+])
+def test_everything_else_is_refused(text):
+    with pytest.raises(TritonEnvError):
+        apply_triton_env(text, {}, {})
+
+
+def test_refusal_end_to_end(tmp_path):
+    """A `triton env` that prints a command: the reference would run it; the
+    replacement stops with status 2 before anything is generated."""
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE
+    from tritonk8ssupervisor_b200.conformance.sandbox import run_in_sandbox
+    from tritonk8ssupervisor_b200.conformance.scenario import Scenario
+    marker = tmp_path / "pwned"
+    sc = Scenario(name="evil", stdin="\n" * 8 + "yes\n", triton_env='export SDC_URL="x"\ntouch %s\n' % marker)
+    obs = run_in_sandbox(rp.REPLACEMENT_ARGV, WORKSPACE_TEMPLATE, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert obs.exit_status == 2 and "refusing to run a command" in obs.stderr
+    assert not marker.exists()
+    assert "terraform/rancher.tf" not in obs.files
+    assert [c.split("|")[0] for c in obs.calls] == ["triton"]

@@ -81,7 +81,8 @@ def sed_print_line(text: str, n: int) -> str:
     """``sed -n "${n}p"`` (setup.sh:536,541)."""
     ls = lines(text)
     if 1 <= n <= len(ls):
-        return ls[n - 1] + "\n"
+        last_unterminated = n == len(ls) and not text.endswith("\n")
+        return ls[n - 1] + ("" if last_unterminated else "\n")   # GNU sed keeps a missing final newline missing
     return ""
 
 
