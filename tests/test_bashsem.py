@@ -1,6 +1,5 @@
 """bashsem restates bash behaviour; here it is checked against the real bash
 (5.2 in this image, present on the GPU box as well)."""
-import os
 import subprocess
 
 import pytest

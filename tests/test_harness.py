@@ -110,7 +110,6 @@ def test_triton_table_cache_changes_only_the_trace():
     """TK8S_CACHE_TRITON=1: byte-identical stdout and files, strictly fewer
     `triton` calls (one `networks`, one `packages`), nothing else reordered."""
     from tritonk8ssupervisor_b200.conformance import replay as rp
-    from tritonk8ssupervisor_b200.conformance.sandbox import Observation
     for sc in CONFIGS:
         doc = harness.golden_for(sc)
         env = dict(rp.REPLACEMENT_ENV, TK8S_CACHE_TRITON="1")

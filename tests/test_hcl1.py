@@ -2,7 +2,7 @@
 import pytest
 
 from tritonk8ssupervisor_b200 import hcl1
-from tritonk8ssupervisor_b200.hcl1 import Body, HCall, HStr, HVar, ListVal, Literal
+from tritonk8ssupervisor_b200.hcl1 import Body, HCall, HStr, HVar, ListVal
 
 
 def test_generated_module_block():

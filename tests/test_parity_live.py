@@ -13,7 +13,7 @@ from oracle.reference_runner import find_reference, reference_sha256, run_refere
 from tritonk8ssupervisor_b200.conformance import replay as rp
 from tritonk8ssupervisor_b200.conformance.catalog import ALL, CONFIGS
 from tritonk8ssupervisor_b200.conformance.sandbox import Observation, run_in_sandbox
-from tritonk8ssupervisor_b200.conformance.scenario import DOC_NETWORKS, Scenario, triton_table
+from tritonk8ssupervisor_b200.conformance.scenario import Scenario, triton_table
 
 pytestmark = pytest.mark.skipif(find_reference() is None, reason="no reference tree (not /root/reference, not oracle/_ref)")
 

@@ -1,7 +1,6 @@
 """Terraform structural validator: accepts what the path generates (against the
 package's modules and, where available, the reference's own), and rejects each
 class of breakage with its own code."""
-import json
 import os
 import shutil
 

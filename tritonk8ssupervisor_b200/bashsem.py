@@ -20,7 +20,7 @@ from __future__ import annotations
 
 import os
 import re
-from typing import Callable, Iterable, List, Optional, Sequence, Tuple
+from typing import Callable, List, Optional, Sequence, Tuple
 
 IFS_WS = " \t\n"
 

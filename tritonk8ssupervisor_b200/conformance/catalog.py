@@ -11,8 +11,7 @@ from __future__ import annotations
 
 from typing import Dict, List
 
-from .scenario import (DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario,
-                       triton_env_text, triton_table)
+from .scenario import DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario, triton_table
 
 YES = "yes\n"
 BLANK8 = "\n" * 8

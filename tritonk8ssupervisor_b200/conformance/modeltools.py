@@ -18,7 +18,7 @@ import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 from .. import bashsem
-from ..runtime import CAPTURE, DEVNULL, INHERIT, TO_STDOUT, Runtime
+from ..runtime import CAPTURE, INHERIT, TO_STDOUT, Runtime
 from ..supervisor import Supervisor
 from .sandbox import Observation, _snapshot, _write
 from .scenario import Scenario

@@ -30,11 +30,11 @@ from __future__ import annotations
 
 import os
 import re
-from typing import Any, List
+from typing import Any
 
 from . import ansiblecheck as ac
 from . import hcl1
-from .hcl1 import Body, HVar, ListVal, Literal
+from .hcl1 import Body, HVar, Literal
 from .report import Finding, Report
 
 CLI_ADVICE = [

@@ -28,7 +28,7 @@ import re
 import subprocess
 import urllib.error
 import urllib.request
-from typing import Any, Callable, Dict, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Tuple
 
 import jinja2
 

@@ -18,9 +18,8 @@ from __future__ import annotations
 
 import os
 import subprocess
-import sys
 import time
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, Optional, Sequence, Tuple
 
 from . import bashsem
 

@@ -8,9 +8,9 @@ same child processes with the same argv in the same order and environment, same
 bytes on stdout and in every generated file, same exit statuses -- including
 the ones that look wrong (exit 0 from the previous-run guard, setup.sh:14-18).
 
-Design, as opposed to the reference's: the eight prompts are data
-(:class:`Prompt` records driven by one loop, where the reference has eight
-copy-pasted blocks), the three Terraform block shapes come from one emitter, and
+Design, as opposed to the reference's: the prompts are data (message, validator,
+error lines, reference line) driven by three small loops where the reference
+has eight copy-pasted blocks, the Terraform block shapes come from one emitter, and
 everything bash does to a string implicitly is an explicit call into
 :mod:`bashsem` / :mod:`textops`.  All I/O goes through a :class:`Runtime`, so the
 same code runs as a CLI and in-process.
@@ -42,7 +42,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 from . import bashsem as sh
 from . import textops as tx
-from .runtime import CAPTURE, DEVNULL, INHERIT, TO_STDOUT, Runtime, ScriptExit
+from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
 from .tritonenv import TritonEnvError, apply_triton_env
 
 RULE = "#" * 80

@@ -9,7 +9,7 @@ reference uses are covered (cited per function).
 from __future__ import annotations
 
 import re
-from typing import Callable, List
+from typing import List
 
 from .bashsem import c_sort_key
 

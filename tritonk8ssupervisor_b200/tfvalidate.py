@@ -40,7 +40,7 @@ from typing import Any, Dict, List, Optional, Tuple
 
 from . import hcl1
 from .hcl1 import Body, HCall, HVar, Item, ListVal, Literal
-from .report import Finding, Report
+from .report import Report
 
 # interpolation functions of Terraform 0.9 (config/interpolate_funcs.go)
 FUNCTIONS = {

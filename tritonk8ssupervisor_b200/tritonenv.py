@@ -9,7 +9,7 @@ That is the one deliberate narrowing of the boundary ("Deviation
 from __future__ import annotations
 
 import re
-from typing import Dict, List, Tuple
+from typing import Dict, List
 
 _NAME = re.compile(r"[A-Za-z_][A-Za-z0-9_]*\Z")
 
