@@ -11,8 +11,9 @@ real tools:
        files, child-process trace);
  (ii)  terraform -- the structural validator accepts the generated
        ``terraform/rancher.tf`` together with the two modules it instantiates,
-       and the plan holds one ``triton_machine`` per module block with the
-       resolved inputs;
+       the plan holds one ``triton_machine`` per module block with the resolved
+       inputs, and ``apply`` against the mocked provider (tfmock: the modules'
+       own local-exec lines, interpreted) writes the IP files the run recorded;
  (iii) ansible -- the structural checker accepts ``clusterUp.yml`` + roles with
        the generated vars file, ``ansible.cfg`` is valid, and the inventory
        rendered from the generated ``ansible/hosts`` equals the expected
@@ -94,7 +95,8 @@ def check_generated_tree(workspace: str, obs: Observation, res: ConfigResult) ->
     if not plan_ok:
         res.details.append("terraform: plan does not hold one triton_machine per generated module block: %r vs %r"
                            % ([p["address"] for p in planned], names))
-    res.terraform = tf.ok and plan_ok and len(planned) >= 2
+    mock_ok = _mock_apply_agrees(workspace, obs, res) if tf.ok else False
+    res.terraform = tf.ok and plan_ok and mock_ok and len(planned) >= 2
 
     hosts_file = os.path.join(workspace, "ansible", "hosts")
     try:
@@ -112,6 +114,33 @@ def check_generated_tree(workspace: str, obs: Observation, res: ConfigResult) ->
     cfg = ansiblecheck.check_ansible_cfg(os.path.join(workspace, "ansible", "ansible.cfg"))
     res.details += ["ansible: %s" % f for f in an.errors + cfg.errors]
     res.ansible = an.ok and cfg.ok
+
+
+def _mock_apply_agrees(workspace: str, obs: Observation, res: ConfigResult) -> bool:
+    """`terraform apply` against the mocked provider (tfmock), in a scratch copy of
+    terraform/: interpreting the modules' own local-exec lines must give the IP
+    files the run recorded."""
+    import shutil
+    import tempfile
+
+    from .. import tfmock
+    tmp = tempfile.mkdtemp(prefix="tk8s-tfmock-")
+    try:
+        tf = shutil.copytree(os.path.join(workspace, "terraform"), os.path.join(tmp, "terraform"),
+                             ignore=shutil.ignore_patterns("*.ip", "terraform.tfstate*", ".terraform*"))
+        machines, rep = tfmock.apply(tf)
+        got = {}
+        for name in ("masters.ip", "hosts.ip"):
+            p = os.path.join(tf, name)
+            got["terraform/" + name] = open(p).read() if os.path.exists(p) else None
+        want = {k: obs.files.get(k) for k in got}
+        if not rep.ok or got != want:
+            res.details.append("terraform: mock apply gives %r, the run recorded %r (%s)"
+                               % (got, want, "; ".join(str(f) for f in rep.errors)))
+            return False
+        return True
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
 
 
 def run_config(doc: dict, argv: Optional[Sequence[str]] = None, extra_env: Optional[Dict[str, str]] = None,

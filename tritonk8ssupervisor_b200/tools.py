@@ -5,6 +5,7 @@
     init DIR               lay down the package's workspace (terraform/, ansible/) in DIR
     validate [DIR]         `terraform validate` stand-in on DIR/terraform        (exit 1 on errors)
     plan [DIR]             resource instances + resolved inputs, as JSON
+    apply-mock [DIR]       `terraform apply` against a mocked Triton provider (writes masters.ip/hosts.ip)
     syntax-check [DIR]     `ansible-playbook --syntax-check` stand-in on DIR/ansible/clusterUp.yml
     inventory [DIR]        `ansible-inventory -i DIR/ansible/hosts --list`
     lint [DIR]             advisory modern-dialect report (never fails)
@@ -42,7 +43,7 @@ def _inventory(root: str) -> Optional[inventory.Inventory]:
 def main(argv: Optional[List[str]] = None, out=sys.stdout) -> int:
     ap = argparse.ArgumentParser(prog="tritonk8ssupervisor_b200.tools", description=__doc__,
                                  formatter_class=argparse.RawDescriptionHelpFormatter)
-    ap.add_argument("command", choices=["init", "validate", "plan", "syntax-check", "inventory", "lint", "dry-run", "conformance"])
+    ap.add_argument("command", choices=["init", "validate", "plan", "apply-mock", "syntax-check", "inventory", "lint", "dry-run", "conformance"])
     ap.add_argument("dir", nargs="?", default=".")
     args = ap.parse_args(argv)
     root = args.dir
@@ -65,6 +66,13 @@ def main(argv: Optional[List[str]] = None, out=sys.stdout) -> int:
         json.dump(tfvalidate.plan(os.path.join(root, "terraform")), out, indent=1)
         out.write("\n")
         return 0
+    if args.command == "apply-mock":
+        from . import tfmock
+        machines, rep = tfmock.apply(os.path.join(root, "terraform"))
+        for m in machines:
+            out.write("%s: created (primaryip %s)\n" % (m.address, m.computed.get("primaryip")))
+        _print_report(rep, out)
+        return 0 if rep.ok else 1
     if args.command == "syntax-check":
         try:
             inv = _inventory(root)
