@@ -105,6 +105,20 @@ def step_reference(docs: List[dict], ref_root: str) -> List[harness.ConfigResult
     return out
 
 
+def median_wall_ms(argv, env, workspace_src: str, docs: List[dict], runs: int, overrides: bool) -> Dict[str, float]:
+    """wall clock around the subprocess alone (no checks), fresh
+    sandbox per run, median of ``runs`` runs per config."""
+    out = {}
+    for doc in docs:
+        sc = Scenario.from_json(doc["scenario"])
+        walls = []
+        for _ in range(runs):
+            with Sandbox(workspace_src, sc, input_overrides=doc["inputs"] if overrides else None) as sbx:
+                walls.append(sbx.run(argv, env).wall_s)
+        out[sc.name] = round(1e3 * statistics.median(walls), 2)
+    return out
+
+
 def timed(fn, steps: int, warmup: int):
     """(results of the last step, [seconds per timed step])."""
     results = None
@@ -178,6 +192,8 @@ def main(argv=None) -> int:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--median-runs", type=int, default=20,
+                    help="runs per config for the per-config median wall times (SURVEY.md §8d asks for >= 20)")
     args = ap.parse_args(argv)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     docs = [harness.golden_for(sc) for sc in CONFIGS]
@@ -243,13 +259,18 @@ def main(argv=None) -> int:
     if ranks.rank == 0 and args.gpus == 1 and ref_root is not None:
         ref_results, ref_times = timed(lambda: step_reference(docs, ref_root), 3, 1)
         ref_ms = 1e3 * statistics.mean(ref_times)
+        from oracle.reference_runner import REFERENCE_ARGV
         cpu_baseline = {"value": harness.pass_rate(ref_results), "unit": UNIT, "cores": 1, "kind": "reference",
-                        "sample": "all 5 configs x 3 steps, unmodified setup.sh under bash in the stub sandbox",
-                        "ms_per_step": ref_ms, "configs_per_s": len(docs) / (ref_ms / 1e3)}
+                        "sample": "all 5 configs x 3 steps (with checks) + %d bare runs per config, unmodified setup.sh "
+                                  "under bash in the stub sandbox" % args.median_runs,
+                        "ms_per_step": ref_ms, "configs_per_s": len(docs) / (ref_ms / 1e3),
+                        "median_run_ms_per_config": median_wall_ms(REFERENCE_ARGV, None, ref_root, docs, args.median_runs, False)}
     else:
         cpu_baseline = {"value": None, "unit": UNIT, "cores": 1, "kind": "reference",
                         "sample": "not run (rank != 0, N > 1, or no reference tree on this machine)"}
 
+    ours_median = (median_wall_ms(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, harness.WORKSPACE_TEMPLATE, docs,
+                                  args.median_runs, True) if ranks.rank == 0 and args.gpus == 1 else None)
     extension = harness.extension_count_scaling(10) if ranks.rank == 0 else None
     if ranks.rank == 0:
         line = dict(base, value=rate, ms_per_step=ms, configs_per_s=ranks.world * len(docs) / (ms / 1e3),
@@ -258,6 +279,7 @@ def main(argv=None) -> int:
                          "configs_per_s": ranks.world * len(docs) / (e2e_ms / 1e3),
                          "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                          "stdin_bytes_per_step": stdin_bytes, "output_bytes_per_step": out_bytes,
+                         "median_run_ms_per_config": ours_median,
                          "note": "public CLI as a child process, stub tools as child processes; 1 timed run per config (+ an untimed second pass for determinism); no device"},
                     cpu_baseline=cpu_baseline,
                     extension_config5b={k: extension[k] for k in ("ok", "n_workers", "modules", "planned_machines",

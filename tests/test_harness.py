@@ -63,7 +63,7 @@ def test_structural_failure_is_detected(tmp_path):
 
 
 def test_bench_line_contract():
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0"],
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0", "--median-runs", "2"],
                        capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert p.returncode == 0, p.stderr
     lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
@@ -75,6 +75,7 @@ def test_bench_line_contract():
     assert d["value"] == 1.0 and d["e2e"]["value"] == 1.0
     assert d["gpu_launches"] == 0 and d["roofline"]["frac"] is None and d["vs_baseline"] is None
     assert "workload" in d["config"]
+    assert set(d["e2e"]["median_run_ms_per_config"]) == {c.name for c in CONFIGS}
 
 
 def test_bench_reference_arm(ref_root):
