@@ -35,6 +35,7 @@ variable it reads must be defined somewhere (vars file, ``register``, loop
 """
 from __future__ import annotations
 
+import functools
 import os
 import re
 from typing import Any, Dict, Iterable, List, Optional, Set, Tuple
@@ -138,7 +139,10 @@ for _n in ANSIBLE_TESTS:
 # ---------------------------------------------------------------------------
 # YAML loading with duplicate-key detection
 # ---------------------------------------------------------------------------
-class _Loader(yaml.SafeLoader):
+_BaseLoader = getattr(yaml, "CSafeLoader", yaml.SafeLoader)   # libyaml parser when the wheel has it
+
+
+class _Loader(_BaseLoader):
     pass
 
 
@@ -153,7 +157,7 @@ def _construct_mapping(loader: _Loader, node: yaml.MappingNode, deep: bool = Fal
         if key in seen:
             loader.duplicates.append((key, key_node.start_mark.line + 1))  # type: ignore[attr-defined]
         seen[key] = key_node.start_mark.line + 1
-    return yaml.SafeLoader.construct_mapping(loader, node, deep=deep)
+    return yaml.constructor.SafeConstructor.construct_mapping(loader, node, deep=deep)
 
 
 _Loader.add_constructor(yaml.resolver.BaseResolver.DEFAULT_MAPPING_TAG, _construct_mapping)
@@ -295,24 +299,36 @@ def _strings_in(value: Any) -> Iterable[str]:
             yield from _strings_in(v)
 
 
-def jinja_names(source: str, where: str, report: Report) -> Set[str]:
-    """Parse a template; report syntax errors and unknown filters/tests; return
-    the free variables it reads."""
+@functools.lru_cache(maxsize=4096)
+def _analyse_template(source: str) -> Tuple[Tuple[Tuple[str, str], ...], frozenset]:
+    """((code, message), ...) and the free variables of one template source."""
+    if "{{" not in source and "{%" not in source and "{#" not in source:
+        return (), frozenset()
     try:
         ast = _JENV.parse(source)
     except jinja2.TemplateSyntaxError as exc:
-        report.error("jinja-syntax", where, "%s in %r" % (exc.message, source))
-        return set()
+        return (("jinja-syntax", "%s in %r" % (exc.message, source)),), frozenset()
+    problems = []
     for node in ast.find_all(jinja2.nodes.Filter):
         if node.name not in KNOWN_FILTERS:
-            report.error("jinja-filter", where, "unknown filter %r in %r" % (node.name, source))
+            problems.append(("jinja-filter", "unknown filter %r in %r" % (node.name, source)))
     for node in ast.find_all(jinja2.nodes.Test):
         if node.name not in KNOWN_TESTS:
-            report.error("jinja-filter", where, "unknown test %r in %r" % (node.name, source))
+            problems.append(("jinja-filter", "unknown test %r in %r" % (node.name, source)))
     try:
-        return set(jinja2.meta.find_undeclared_variables(ast))
+        names = frozenset(jinja2.meta.find_undeclared_variables(ast))
     except jinja2.TemplateAssertionError:
-        return set()  # unknown filter/test, already reported above
+        names = frozenset()  # unknown filter/test, already recorded above
+    return tuple(problems), names
+
+
+def jinja_names(source: str, where: str, report: Report) -> Set[str]:
+    """Parse a template; report syntax errors and unknown filters/tests; return
+    the free variables it reads."""
+    problems, names = _analyse_template(source)
+    for code, message in problems:
+        report.error(code, where, message)
+    return set(names)
 
 
 def expression_names(expr: Any, keyword: str, where: str, report: Report) -> Set[str]:

@@ -23,4 +23,9 @@ from .supervisor import Supervisor
 
 def main(argv: Optional[Sequence[str]] = None, root: str = ".") -> int:
     args = list(sys.argv[1:] if argv is None else argv)
-    return Supervisor(HostRuntime(root=root), program="setup.sh").main(args)
+    try:
+        return Supervisor(HostRuntime(root=root), program="setup.sh").main(args)
+    except KeyboardInterrupt:
+        return 130          # what a shell script reports after SIGINT
+    except BrokenPipeError:
+        return 141          # ... and after SIGPIPE on a closed stdout

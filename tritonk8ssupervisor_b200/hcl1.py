@@ -27,6 +27,7 @@ AST
 from __future__ import annotations
 
 import dataclasses
+import os
 import re
 from typing import Any, Iterator, List, Optional, Tuple, Union
 
@@ -568,9 +569,23 @@ def parse(src: str, filename: str = "<hcl>") -> Body:
     return Parser(src, filename).parse()
 
 
+_FILE_CACHE: dict = {}
+
+
 def parse_file(path: str) -> Body:
-    with open(path, encoding="utf-8") as fh:
-        return parse(fh.read(), path)
+    """Parse a file; results are memoised on (path, size, mtime) -- validate, plan
+    and the mock apply all walk the same few module files.  The tree is treated
+    as read-only by every consumer."""
+    st = os.stat(path)
+    key = (path, st.st_size, st.st_mtime_ns)
+    hit = _FILE_CACHE.get(key)
+    if hit is None:
+        with open(path, encoding="utf-8") as fh:
+            hit = parse(fh.read(), path)
+        if len(_FILE_CACHE) > 256:
+            _FILE_CACHE.clear()
+        _FILE_CACHE[key] = hit
+    return hit
 
 
 def templates_in(value: Any) -> Iterator[Tuple[List[Any], int]]:
