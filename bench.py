@@ -153,9 +153,9 @@ def sample_clocks() -> Optional[Dict[str, Any]]:
 # (SURVEY.md §8e), so N ranks are N independent CPU replicas of the same pass
 # ---------------------------------------------------------------------------
 class Ranks:
-    def __init__(self) -> None:
+    def __init__(self, distributed: bool = True) -> None:
         self.rank = int(os.environ.get("RANK", "0"))
-        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1")) if distributed else 1
         self.dist = None
         if self.world > 1:
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -197,7 +197,9 @@ def main(argv=None) -> int:
     args = ap.parse_args(argv)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     docs = [harness.golden_for(sc) for sc in CONFIGS]
-    ranks = Ranks()
+    if args.impl == "reference" and int(os.environ.get("RANK", "0")) != 0:
+        return 0          # under torchrun rank 0 alone runs the reference arm; no process group is formed
+    ranks = Ranks(distributed=args.impl != "reference")
 
     from oracle.reference_runner import find_reference  # the baseline legs are the only users of oracle/
     ref_root = find_reference()
@@ -212,9 +214,6 @@ def main(argv=None) -> int:
                          "note": NOT_APPLICABLE}}
 
     if args.impl == "reference":
-        if ranks.rank != 0:
-            ranks.close()
-            return 0
         if ref_root is None:
             print(json.dumps({"impl": "reference", "unavailable": "no reference tree: neither /root/reference nor the staged oracle/_ref/reference"}))
             return 0

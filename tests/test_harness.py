@@ -124,3 +124,19 @@ def test_triton_table_cache_changes_only_the_trace():
         triton = [c for c in got.calls if c.startswith("triton|")]
         assert triton == ["triton|.|env", "triton|.|networks -oname,id", "triton|.|packages -oname,id"]
         assert len([c for c in want.calls if c.startswith("triton|")]) >= 6      # env + 2 menus + 3 default resolutions
+
+
+def test_bench_reference_arm_under_torchrun(ref_root):
+    """N > 1 reference arm: rank 0 alone runs and prints, the others exit 0 (no process group, no hang)."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "bench.py"),
+                        "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1 and json.loads(lines[0])["impl"] == "reference"
