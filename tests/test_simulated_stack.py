@@ -62,3 +62,19 @@ def test_simulated_terraform_refuses_a_broken_config(tmp_path):
     p.write_text(p.read_text().replace('variable "package"', 'variable "pkg"'))
     obs = _run(str(ws), rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV)
     assert obs.exit_status == 1 and "arg-unknown" in obs.stdout and "terraform/masters.ip" not in obs.files
+
+
+def test_bootstrap_that_forgets_root_keys_makes_the_playbook_fail(tmp_path):
+    """Drop the line that copies the keys to root: terraform still succeeds, the
+    playbook cannot reach the nodes, setup dies with ansible-playbook's status."""
+    import shutil
+    ws = tmp_path / "ws"
+    shutil.copytree(WORKSPACE_TEMPLATE, ws)
+    p = ws / "terraform/host/machine.tf"
+    text = p.read_text()
+    line = [l for l in text.split("\n") if "authorized_keys /root" in l][0]
+    p.write_text(text.replace(line + "\n", ""))
+    obs = _run(str(ws), rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV)
+    assert obs.exit_status == 2
+    assert "UNREACHABLE: Permission denied (publickey) for root" in obs.stdout
+    assert "Apply complete! Resources: 4 added" in obs.stdout and "Congratulations" not in obs.stdout

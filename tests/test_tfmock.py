@@ -78,3 +78,37 @@ def test_failing_local_exec_stops_the_apply(tmp_path):
     p.write_text(p.read_text().replace(">> hosts.ip", ">> /nonexistent-dir/hosts.ip"))
     machines, report = tfmock.apply(str(tf))
     assert "local-exec" in report.codes("error") and [m.module for m in machines] == ["kubemaster", "kubenode1"]
+
+
+@pytest.mark.parametrize("label,src", _sources(), ids=[s[0] for s in _sources()])
+def test_bootstrap_makes_machines_usable_by_ansible(tmp_path, label, src):
+    """main.tf:21-26: after the remote-exec lines root can log in with the operator's key and python exists."""
+    tf = tmp_path / "terraform"
+    shutil.copytree(src, tf)
+    (tf / "rancher.tf").write_text(harness.golden_for(CONFIGS[1])["expected"]["files"]["terraform/rancher.tf"])
+    machines, report = tfmock.apply(str(tf))
+    assert report.ok
+    for m in machines:
+        st = tfmock.bootstrap_state(m)
+        assert st["ansible_ready"], st
+        assert st["waited_s"] == 30 and st["packages"] == ["python-minimal"] and st["unmodelled"] == []
+
+
+@pytest.mark.parametrize("old,new,needle", [
+    ('"sudo apt-get update",\n', "", "before apt-get update"),
+    ("-y", "", "would wait for confirmation"),
+    ('user        = "ubuntu"', 'user        = "root"', "only admits 'ubuntu'"),
+])
+def test_broken_bootstrap_is_noticed(tmp_path, old, new, needle):
+    tf = tmp_path / "terraform"
+    shutil.copytree(os.path.join(harness.WORKSPACE_TEMPLATE, "terraform"), tf)
+    (tf / "rancher.tf").write_text(harness.golden_for(CONFIGS[0])["expected"]["files"]["terraform/rancher.tf"])
+    p = tf / "host" / "machine.tf"
+    text = p.read_text()
+    assert old in text
+    p.write_text(text.replace(old, new, 1))
+    machines, report = tfmock.apply(str(tf))
+    host = [m for m in machines if m.rname == "host"][0]
+    st = tfmock.bootstrap_state(host)
+    assert not st["ansible_ready"] and any(needle in e for e in st["errors"]), st
+    assert tfmock.bootstrap_state([m for m in machines if m.rname == "master"][0])["ansible_ready"]

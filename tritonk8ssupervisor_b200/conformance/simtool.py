@@ -51,8 +51,13 @@ def terraform(args) -> int:
         return 0 if rep.ok else 1
     if sub == "apply":
         machines, rep = tfmock.apply(".")
+        import json
+        boot = {}
         for m in machines:
             print("%s: Creation complete (primaryip = %s)" % (m.address, m.computed["primaryip"]))
+            boot[m.computed["primaryip"]] = tfmock.bootstrap_state(m)
+        with open(os.path.join(os.environ["TK8S_STUB_STATE"], "bootstrap.json"), "w", encoding="utf-8") as fh:
+            json.dump(boot, fh)
         for f in rep.errors:
             print("Error applying plan: %s" % f)
         if rep.ok:
@@ -83,8 +88,23 @@ def ansible_playbook(args) -> int:
     with open(os.path.join("roles", "ranchermaster", "vars", "vars.yml"), encoding="utf-8") as fh:
         master = str((yaml.safe_load(fh) or {}).get("master", ""))
     os.makedirs("tmp", exist_ok=True)
+    # machines are usable only if terraform's bootstrap made them so (tfmock.bootstrap_state)
+    unreachable = {}
+    boot_file = os.path.join(os.environ["TK8S_STUB_STATE"], "bootstrap.json")
+    if os.path.isfile(boot_file):
+        import json
+        with open(boot_file, encoding="utf-8") as fh:
+            boot = json.load(fh)
+        for host in inv.host_order:
+            st = boot.get(host)
+            if st is None:
+                unreachable[host] = "%s: UNREACHABLE: no such machine was created" % host
+            elif not st["root_login"]:
+                unreachable[host] = "%s: UNREACHABLE: Permission denied (publickey) for root" % host
+            elif not st["python"]:
+                unreachable[host] = "%s: MODULE FAILURE: /usr/bin/python: not found" % host
     with ranchermock.RancherMock(public_host=master) as mock:
-        run = roledryrun.DryRun(playbook, inv, {"%s:8080" % master: mock.address}).run()
+        run = roledryrun.DryRun(playbook, inv, {"%s:8080" % master: mock.address}, unreachable=unreachable).run()
     print("PLAY RECAP *********************************************************************")
     for host, c in run.recap().items():
         print("%-26s : ok=%-4d changed=%-4d unreachable=0    failed=%d" % (host, c["ok"], c["changed"], c["failed"]))

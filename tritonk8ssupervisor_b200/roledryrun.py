@@ -305,7 +305,8 @@ class DryRun:
     holds registered variables."""
 
     def __init__(self, playbook: str, inventory: Inventory, address_map: Dict[str, str],
-                 hosts: Optional[Dict[str, SimHost]] = None, rancher_up_after: int = 2):
+                 hosts: Optional[Dict[str, SimHost]] = None, rancher_up_after: int = 2,
+                 unreachable: Optional[Dict[str, str]] = None):
         self.playbook = os.path.abspath(playbook)
         self.dir = os.path.dirname(self.playbook)
         self.inventory = inventory
@@ -316,7 +317,8 @@ class DryRun:
         self.templar = Templar()
         self.events: List[Tuple[str, str, str, str]] = []
         self.hostvars: Dict[str, Dict[str, Any]] = {h: {} for h in self.hosts}
-        self.failed_hosts: Dict[str, str] = {}
+        #: hosts Ansible cannot use at all (no root login, no python): host -> reason
+        self.failed_hosts: Dict[str, str] = dict(unreachable or {})
         self.slept_s = 0
 
     # -- variables -----------------------------------------------------------

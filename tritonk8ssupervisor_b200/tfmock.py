@@ -193,3 +193,58 @@ def apply(root_dir: str, allocator: Optional[Callable[[str, str, Dict[str, Any]]
                             return machines + [m], report
             machines.append(m)
     return machines, report
+
+
+# ---------------------------------------------------------------------------
+# what the remote-exec bootstrap leaves on the machine
+# ---------------------------------------------------------------------------
+def bootstrap_state(machine: Machine) -> Dict[str, Any]:
+    """Interpret the ``remote-exec`` scripts of a machine against a small model
+    of the ``ubuntu-certified-16.04`` image (docs/manual-setup.md:9-40): only the
+    user ``ubuntu`` can log in and holds the keys given as ``root_authorized_keys``,
+    root has none, there is no python, and the apt lists are empty until
+    ``apt-get update``.  The playbook needs the opposite (``remote_user: root``,
+    ansible/clusterUp.yml:4,10,20, and python for every module), so this says
+    whether the bootstrap lines of main.tf:21-26 achieve it."""
+    st: Dict[str, Any] = {"root_login": False, "python": False, "apt_updated": False, "waited_s": 0,
+                          "packages": [], "errors": [], "unmodelled": []}
+    for script in machine.remote_exec:
+        conn = script.get("connection") or {}
+        if conn.get("user") != "ubuntu":
+            st["errors"].append("connection as %r: the image only admits 'ubuntu' before the bootstrap" % conn.get("user"))
+            continue
+        if conn.get("host") != machine.computed.get("primaryip"):
+            st["errors"].append("connection host %r is not the machine's primaryip" % conn.get("host"))
+            continue
+        if not conn.get("private_key"):
+            st["errors"].append("connection without private_key (agent is off)")
+            continue
+        for cmd in script.get("inline") or []:
+            words = str(cmd).split()
+            if words[:1] == ["sudo"]:
+                words = words[1:]
+            if words[:1] == ["sleep"] and len(words) == 2 and words[1].isdigit():
+                st["waited_s"] += int(words[1])
+            elif words[:1] in (["cp"], ["install"]):
+                paths = [w for w in words[1:] if w.startswith("/")]
+                if len(paths) == 2 and paths[0] == "/home/ubuntu/.ssh/authorized_keys" \
+                        and paths[1] in ("/root/.ssh/", "/root/.ssh", "/root/.ssh/authorized_keys"):
+                    st["root_login"] = True
+                else:
+                    st["unmodelled"].append(cmd)
+            elif words[:2] == ["apt-get", "update"]:
+                st["apt_updated"] = True
+            elif words[:2] == ["apt-get", "install"]:
+                pkgs = [w for w in words[2:] if not w.startswith("-")]
+                if "-y" not in words and "--yes" not in words:
+                    st["errors"].append("%r would wait for confirmation (no -y)" % cmd)
+                elif not st["apt_updated"]:
+                    st["errors"].append("%r before apt-get update: package lists are empty on a fresh image" % cmd)
+                else:
+                    st["packages"] += pkgs
+                    if any(p in ("python-minimal", "python", "python2.7") for p in pkgs):
+                        st["python"] = True
+            else:
+                st["unmodelled"].append(cmd)
+    st["ansible_ready"] = bool(st["root_login"] and st["python"] and not st["errors"])
+    return st
