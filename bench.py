@@ -192,6 +192,10 @@ def main(argv=None) -> int:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--triton-latency-ms", type=int, default=0,
+                    help="opt-in latency MODEL: make every stubbed `triton` call take this long (a real call is a node "
+                         "start-up plus a CloudAPI round trip) and time config 2 under the reference, the replacement, "
+                         "and the replacement with TK8S_CACHE_TRITON=1")
     ap.add_argument("--median-runs", type=int, default=20,
                     help="runs per config for the per-config median wall times (SURVEY.md §8d asks for >= 20)")
     args = ap.parse_args(argv)
@@ -270,6 +274,9 @@ def main(argv=None) -> int:
 
     ours_median = (median_wall_ms(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, harness.WORKSPACE_TEMPLATE, docs,
                                   args.median_runs, True) if ranks.rank == 0 and args.gpus == 1 else None)
+    latency_model = None
+    if args.triton_latency_ms > 0 and ranks.rank == 0:
+        latency_model = triton_latency_model(docs[1], args.triton_latency_ms, ref_root)
     extension = harness.extension_count_scaling(10) if ranks.rank == 0 else None
     if ranks.rank == 0:
         line = dict(base, value=rate, ms_per_step=ms, configs_per_s=ranks.world * len(docs) / (ms / 1e3),
@@ -283,9 +290,35 @@ def main(argv=None) -> int:
                     cpu_baseline=cpu_baseline,
                     extension_config5b={k: extension[k] for k in ("ok", "n_workers", "modules", "planned_machines",
                                                                    "inventory_hosts", "rancher_tf_bytes", "size_law")})
+        if latency_model is not None:
+            line["triton_latency_model"] = latency_model
         print(json.dumps(line))
     ranks.close()
     return 0
+
+
+def triton_latency_model(doc: dict, ms: int, ref_root: Optional[str], runs: int = 3) -> Dict[str, Any]:
+    """A MODEL, not a measurement of CloudAPI: each stubbed `triton` call sleeps ``ms``.
+    Shows what the per-index re-fetching of setup.sh:536,541 costs and what the
+    opt-in table cache saves; files are byte-identical in all three arms."""
+    sc = Scenario.from_json(doc["scenario"])
+
+    def med(argv, env, src, overrides):
+        walls, calls = [], 0
+        for _ in range(runs):
+            with Sandbox(src, sc, input_overrides=doc["inputs"] if overrides else None, latency_ms={"triton": ms}) as sbx:
+                obs = sbx.run(argv, env)
+                walls.append(obs.wall_s)
+                calls = len([c for c in obs.calls if c.startswith("triton|")])
+        return {"median_run_ms": round(1e3 * statistics.median(walls), 1), "triton_calls": calls}
+    out: Dict[str, Any] = {"model": "every `triton` call takes %d ms" % ms, "config": sc.name,
+                           "replacement": med(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, harness.WORKSPACE_TEMPLATE, True),
+                           "replacement_cached": med(rp.REPLACEMENT_ARGV, dict(rp.REPLACEMENT_ENV, TK8S_CACHE_TRITON="1"),
+                                                     harness.WORKSPACE_TEMPLATE, True)}
+    if ref_root is not None:
+        from oracle.reference_runner import REFERENCE_ARGV
+        out["reference"] = med(REFERENCE_ARGV, None, ref_root, False)
+    return out
 
 
 if __name__ == "__main__":

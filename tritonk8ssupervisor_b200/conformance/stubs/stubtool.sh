@@ -31,6 +31,13 @@ case "$tool" in
         ;;
 esac
 
+# modelled latency (milliseconds) of a tool that sits on a network round trip:
+# a file latency_ms/<tool>.  /bin/sleep by absolute path: `sleep` on PATH is a stub.
+if [ -f "$S/latency_ms/$tool" ]; then
+    ms=$(cat "$S/latency_ms/$tool")
+    /bin/sleep "$(printf '%d.%03d' $((ms / 1000)) $((ms % 1000)))"
+fi
+
 # scripted failure: a file fail/<tool>-<first arg> holding the exit status
 sub=${1:-}
 if [ -f "$S/fail/$tool-$sub" ]; then
