@@ -178,6 +178,21 @@ EDGE: List[Scenario] = [
              note="banner URLs come from masters.ip and the id the playbook stored"),
     Scenario(name="env_id_missing", stdin=BLANK8 + YES, pre_remove=["ansible/tmp/kubernetes_environment.id"],
              note="no stored id: cat fails inside $(...), URLs have an empty id"),
+    # --- a workspace that is not what setup expects ------------------------------
+    Scenario(name="ws_no_terraform_dir", stdin=BLANK8 + YES, pre_remove=["terraform"],
+             note="no terraform/: the first write of rancher.tf fails (message names line 188), exit 1"),
+    Scenario(name="ws_no_ansible_dir", stdin=BLANK8 + YES, pre_remove=["ansible"],
+             note="no ansible/: machines are provisioned, then `echo >> ansible/hosts` fails (line 123), exit 1"),
+    Scenario(name="ws_no_vars_dir", stdin=BLANK8 + YES, pre_remove=["ansible/roles/ranchermaster/vars"],
+             note="inventory written, vars.yml cannot be (line 129), exit 1"),
+    Scenario(name="ws_hosts_is_a_directory", stdin=BLANK8 + YES, pre_files={"ansible/hosts/keep": ""},
+             note="`rm -f ansible/hosts` on a directory fails silently (2>/dev/null) and errexit ends the run"),
+    Scenario(name="ws_config_is_a_directory", stdin="yes\n" + BLANK8 + YES, pre_files={"config/keep": ""},
+             note="a directory named config counts as an old configuration; clean removes it"),
+    Scenario(name="ws_clean_tmp_is_a_file", args=["-c"], stdin="yes\n", pre_files={"tmp": "a file\n"},
+             note="clean writes the rewritten ansible.cfg through ./tmp: an existing file of that name is overwritten and moved"),
+    Scenario(name="ws_clean_without_ansible_dir", args=["-c"], stdin="yes\n", pre_remove=["ansible"],
+             note="clean with no ansible/: sed fails quietly, an empty ./tmp is left behind"),
     # --- tools that are not installed (bash: "command not found", status 127) ---
     Scenario(name="missing_triton", stdin="yes\n", missing_tools=["triton"],
              note="no triton CLI: eval of nothing, empty SDC_*, menus empty; the first ssh file 'matches' the empty id"),

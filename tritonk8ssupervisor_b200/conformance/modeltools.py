@@ -211,7 +211,9 @@ class ModelSandbox:
             _write(os.path.join(ssh, "known_hosts"), scenario.known_hosts)
         for rel in scenario.pre_remove:
             p = os.path.join(self.workspace, rel)
-            if os.path.exists(p):
+            if os.path.isdir(p) and not os.path.islink(p):
+                shutil.rmtree(p)
+            elif os.path.lexists(p):
                 os.remove(p)
         for rel, content in scenario.pre_files.items():
             _write(os.path.join(self.workspace, rel), content)

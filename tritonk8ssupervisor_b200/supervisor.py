@@ -110,15 +110,17 @@ class Supervisor:
         """Positional parameters produced by an unquoted ``$VALUE`` argument."""
         return sh.expand_unquoted(value, self.rt.root)
 
-    def append_line(self, rel: str, line: str) -> None:
-        """``echo "<line>" >> rel``; a failing redirection ends the script (errexit)."""
+    def append_line(self, rel: str, line: str, lineno: int = 0) -> None:
+        """``echo "<line>" >> rel``; a failing redirection ends the script (errexit).
+        ``lineno`` is the reference line, which bash names in its message."""
         try:
             self.rt.append_text(rel, sh.echo_builtin([line]))
         except OSError as exc:
-            self._redirect_failed(rel, exc)
+            self._redirect_failed(rel, exc, lineno)
 
-    def _redirect_failed(self, rel: str, exc: OSError) -> None:
-        self.rt.err("%s: %s: %s\n" % (self.program, rel, exc.strerror))
+    def _redirect_failed(self, rel: str, exc: OSError, lineno: int = 0) -> None:
+        where = self.at(lineno) if lineno else self.program
+        self.rt.err("%s: %s: %s\n" % (where, rel, exc.strerror))
         raise ScriptExit(1)
 
     def cat_subst(self, rel: str) -> str:
@@ -219,7 +221,7 @@ class Supervisor:
         v["RANCHER_MASTER_NETWORKS"] = ""
         v["KUBERNETES_NODE_NETWORKS"] = ""
         v["HOST_PACKAGE"] = ""
-        self.append_line("config", "ANSIBLE_HOST_KEY_CHECKING=False")
+        self.append_line("config", "ANSIBLE_HOST_KEY_CHECKING=False", 253)
 
     # ------------------------------------------------------------------
     # a2  setConfigFromTritonENV  (setup.sh:209-239)
@@ -636,7 +638,7 @@ class Supervisor:
             try:
                 self.rt.write_text(rel, sh.echo_builtin([block[0]]))
             except OSError as exc:
-                self._redirect_failed(rel, exc)
+                self._redirect_failed(rel, exc, 188)
             for line in block[1:]:
                 self.append_line(rel, line)
             return
@@ -653,9 +655,11 @@ class Supervisor:
             raise ScriptExit(1)
         self.echo("Creating ansible hosts file and variable files")
         hosts = "ansible/hosts"
-        if rt.exists(hosts):
+        if os.path.isdir(rt.path(hosts)) and not os.path.islink(rt.path(hosts)):
+            raise ScriptExit(1)  # `rm -f` cannot remove a directory (message hidden by 2>/dev/null), errexit
+        if os.path.lexists(rt.path(hosts)):
             os.remove(rt.path(hosts))
-        self.append_line(hosts, "[MASTER]")
+        self.append_line(hosts, "[MASTER]", 123)
         rt.append_text(hosts, rt.read_text("terraform/masters.ip"))
         self.append_line(hosts, "[HOST]")
         rt.append_text(hosts, rt.read_text("terraform/hosts.ip"))
@@ -666,7 +670,7 @@ class Supervisor:
         try:
             rt.write_text(vars_yml, sh.echo_builtin(["master: %s" % master]))
         except OSError as exc:
-            self._redirect_failed(vars_yml, exc)
+            self._redirect_failed(vars_yml, exc, 129)
         self.append_line(vars_yml, 'kubernetes_name: "%s"' % self.unq(v.get("KUBERNETES_NAME", "")))
         self.append_line(vars_yml, 'kubernetes_description: "%s"' % self.unq(v.get("KUBERNETES_DESCRIPTION", "")))
 
