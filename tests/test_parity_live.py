@@ -166,3 +166,27 @@ def test_property_key_discovery(ref_root, names, key_id, data, no_E, env_extra):
     sc = Scenario(name="keys", stdin="\n" * 8 + "yes\nyes\n", ssh_files=files, keygen=keygen, keygen_legacy=legacy,
                   keygen_sha=sha, keygen_no_E=no_E, triton_env=triton_env_text(key_id=key_id) + env_extra)
     assert run_reference(sc, ref_root).diff(ours(sc, ref_root)) == []
+
+
+# --- the operator's environment ---------------------------------------------------
+@pytest.mark.parametrize("scenario,env", [
+    (Scenario(name="env_sdc_preset_triton_env_fails", stdin="\n" * 8 + "yes\n", fail={"triton-env": 1}),
+     {"SDC_URL": "https://preset", "SDC_ACCOUNT": "presetacct", "SDC_KEY_ID": "aa:bb:cc:dd"}),
+    (Scenario(name="env_path_variables_preset", stdin="\n" * 8 + "yes\n"),
+     {"KUBERNETES_NAME": "from env", "HOST_PACKAGE": "envpkg", "RANCHER_MASTER_NETWORKS": "envnet",
+      "KUBERNETES_NUMBER_OF_NODES": "7", "ANSIBLE_HOST_KEY_CHECKING": "True"}),
+    (Scenario(name="env_unrelated_exports", stdin="\n" * 8 + "yes\n"),
+     {"SDC_TESTING": "1", "TRITON_PROFILE": "other", "KUBERNETES_EXTRA": "x y"}),
+], ids=lambda v: v.name if isinstance(v, Scenario) else "env")
+def test_preset_environment(ref_root, scenario, env):
+    """Variables already exported by the operator's shell: assignments to them stay
+    exported (bash), `triton env` overrides or unsets them, and terraform/ansible see
+    exactly the same environment under both implementations (the stubs log it)."""
+    from oracle.reference_runner import REFERENCE_ARGV
+    from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox
+    with Sandbox(ref_root, scenario) as s:
+        theirs = s.run(REFERENCE_ARGV, env)
+    with Sandbox(ref_root, scenario) as s:
+        mine = s.run(rp.REPLACEMENT_ARGV, dict(rp.REPLACEMENT_ENV, **env))
+    assert theirs.diff(mine) == []
+    assert any(c.startswith("  env:") for c in theirs.calls)
