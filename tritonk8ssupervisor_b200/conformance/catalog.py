@@ -62,6 +62,7 @@ _RAN_FILES: Dict[str, str] = {
     "ansible/ansible.cfg.tmp": "stale\n",
     "tmp/scratch.txt": "scratch\n",
     "tmp/sub/deep.txt": "deep\n",
+    "tmp/.hidden": "kept: tmp/* does not match dot files\n",
 }
 
 _PS_TWO_DASHBOARDS = (
@@ -92,6 +93,19 @@ EDGE: List[Scenario] = [
              note="menu order != resolver order when one name is a '-' extension of another (SURVEY §7.4)"),
     Scenario(name="net_uuid_typed_in", stdin=_answers("", "", "", "", "", "31428241-4878-47d6-9fba-9a8436b596a4", "deadbeef", "", "", "yes"),
              note="typing the default UUID is accepted by the [[ == ]] branch; any other string is not"),
+    Scenario(name="net_header_lookalike",
+             networks=triton_table([("NAMEX", "11111111-ID"), ("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4"),
+                                    ("Alonely", ""), ("zeta", "22222222-zeta")]).replace("Alonely            \n", "Alonely\n"),
+             stdin=_answers("", "", "", "", "", "1", "3", "", "yes"),
+             note="a row that looks like the header is dropped from the menu (^NAME.*ID$) but not by the resolver "
+                  "(^NAME *ID$): menu entry 3 (zeta) resolves to NAMEX's id; a row without an id (entry 1) resolves to "
+                  "nothing (awk NF>1)"),
+    Scenario(name="net_three_digit_indices", stdin=_answers("", "", "", "", "", "100,200", "7,8,9", "", "", "", "yes"),
+             note="the regex admits at most two digits per index: '100,200' costs ONE error pair (regex), '7,8,9' three (range)"),
+    Scenario(name="net_default_is_a_pattern", networks=triton_table([("Joyent-SDC-Public", "z?z-9")]),
+             packages=triton_table([("k4-highcpu-kvm-7.75G", "q*q")]),
+             stdin=_answers("", "", "", "", "", "zqz-9", "nomatch", "", "qxyzq", "yes"),
+             note="[[ $answer == $default ]] has an unquoted right-hand side: the default is a *pattern* (setup.sh:345,388,442)"),
     Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
              stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
     Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),
@@ -163,9 +177,17 @@ EDGE: List[Scenario] = [
              ssh_files={"mykey.pub": "P\n", "mykey": "K\n"},
              keygen={"mykey": "2048 MD5:%s fixture@host (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={"mykey": "2048 SHA256:q x (RSA)\n"},
              note="the .pub suffix is stripped before ssh-keygen is asked (setup.sh:217)"),
+    Scenario(name="key_dot_matches_any_char", stdin=BLANK8 + YES,
+             ssh_files={"akeyxpub": "not a key\n", "id_rsa": "K\n", "id_rsa.pub": "P\n"},
+             note="sed 's/.pub$//': the dot is a regex dot, so 'akeyxpub' is asked about as 'akey' (setup.sh:217)"),
     Scenario(name="key_no_ssh_dir_entries", stdin="yes\n", ssh_files={}, note="empty ~/.ssh: key not found"),
     Scenario(name="triton_env_fails", stdin="yes\n", fail={"triton-env": 1},
              note="triton env failing is swallowed by eval \"$(...)\"; empty SDC_* then matches the first non-key"),
+    Scenario(name="stale_ip_files_are_appended_to", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             pre_files={"terraform/masters.ip": "192.0.2.1\n", "terraform/hosts.ip": "192.0.2.2\n"},
+             curl_seq=["not yet\n", "kubernetes\n"],
+             note="IP files of an earlier apply are appended to, not replaced: vars.yml takes the LAST master (tail -1), "
+                  "the banner and the curl URL get both lines, ssh visits the stale node too"),
     # --- below the offline line (setup.sh:117-120,154-159,113) ----------------
     Scenario(name="terraform_get_fails", stdin=BLANK8 + YES, fail={"terraform-get": 3}, note="errexit with terraform's status"),
     Scenario(name="terraform_apply_fails", stdin=BLANK8 + YES, fail={"terraform-apply": 1}, note="errexit with terraform's status"),
@@ -219,6 +241,9 @@ EDGE: List[Scenario] = [
              curl_seq=["502 Bad Gateway\n", "502 Bad Gateway\n", "kubernetes\n"],
              ssh_ps={"10.0.1.1": _PS_TWO_DASHBOARDS, "10.0.1.2": _PS_NONE},
              note="two containers but not 'Service Unavailable': nothing is stopped"),
+    Scenario(name="wait_three_containers", stdin=BLANK8 + YES, curl_seq=["503 Service Unavailable\n", "kubernetes\n"],
+             ssh_ps={"10.0.1.1": _PS_TWO_DASHBOARDS + "9999eeee0000        gcr.io/x   \"/d\"   k8s_kubernetes-dashboard.second\n"},
+             note="three dashboard containers is not 'exactly two': no second curl, nothing stopped (setup.sh:71)"),
     Scenario(name="wait_ssh_fails", stdin=BLANK8 + YES, curl_seq=["nope\n", "kubernetes\n"], ssh_exit={"10.0.1.1": 255},
              note="ssh failures while counting are swallowed by '|| true'"),
     Scenario(name="wait_curl_fails", stdin=BLANK8 + YES, fail={"curl---connect-timeout": 7},

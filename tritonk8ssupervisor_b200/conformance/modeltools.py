@@ -40,6 +40,9 @@ class ModelRuntime(Runtime):
         self.stderr: List[str] = []
         self.calls: List[str] = []
         self._seq: Dict[str, int] = {}
+        self._n_calls = 0
+        self._n_reads = 0
+        self.max_calls = 2000
 
     # -- terminal ----------------------------------------------------------
     def out(self, text: str) -> None:
@@ -55,6 +58,9 @@ class ModelRuntime(Runtime):
         return self._stdin[self._pos - 1]
 
     def read(self, prompt: str) -> Tuple[str, bool]:
+        self._n_reads += 1
+        if self._n_reads > self.max_calls:
+            raise RuntimeError("more than %d reads in one run: runaway prompt loop" % self.max_calls)
         return bashsem.read_builtin(self._next_byte)
 
     # -- clock -------------------------------------------------------------
@@ -68,6 +74,10 @@ class ModelRuntime(Runtime):
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
             stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
         tool, args = argv[0], list(argv[1:])
+        self._n_calls += 1
+        if self._n_calls > self.max_calls:
+            # an implementation that never leaves the wait loop (or a re-prompt loop at EOF) must not hang the caller
+            raise RuntimeError("more than %d tool calls in one run: runaway loop" % self.max_calls)
         if tool in self.sc.missing_tools:
             msg = "%s%s: command not found\n" % (where + ": " if where else "", tool)
             if stderr == INHERIT:
