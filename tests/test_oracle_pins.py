@@ -87,3 +87,20 @@ def test_banner_uses_the_checked_in_environment_id(ref_root):
         env_id = fh.read().strip()
     out = run_reference(CONFIGS[0], ref_root).stdout
     assert "/env/%s/infra/containers" % env_id in out and "/r/projects/%s/kubernetes-dashboard:9090/" % env_id in out
+
+
+def test_oracle_reproduces_the_documented_banner_urls(ref_root):
+    """docs/detailed.md:229-249 quotes the end-of-run banner with placeholders; the three URL
+    templates must be the ones the oracle prints (the prose around them was reworded since:
+    typographic dashes, 'Dashboard' capitalised -- setup.sh:53,88-89 win)."""
+    doc = "\n".join(_doc_lines(ref_root, "docs/detailed.md"))
+    urls = re.findall(r"http://<ip of master>:8080(/[^\n]*?)(?=\n|$)", doc)
+    assert urls == ["/env/<env id>/infra/containers", "/r/projects/<env id>/kubernetes-dashboard:9090/",
+                    "/env/<env id>/kubernetes/kubectl"]
+    out = run_reference(CONFIGS[0], ref_root).stdout
+    for u in urls:
+        assert "http://10.0.0.1:8080" + u.replace("<env id>", "1a7") in out
+    assert "Congratulations, your Kubernetes cluster setup has been complete." in doc and \
+        "Congratulations, your Kubernetes cluster setup has been complete." in out
+    assert "CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!" in doc and \
+        "CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!" in out
