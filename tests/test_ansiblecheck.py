@@ -164,3 +164,26 @@ tier = front
 def test_inventory_errors(text):
     with pytest.raises(inventory.InventoryError):
         inventory.parse_ini(text)
+
+
+def test_blocks_are_walked(ans_dir):
+    (ans_dir / "roles/rancherhost/tasks/main.yml").write_text("""---
+- name: guarded group
+  when: "'x' in master"
+  block:
+    - name: inside
+      command: docker ps -a
+      register: inner
+    - debug:
+        msg: "{{ inner.stdout }} {{ undefined_in_block }}"
+  rescue:
+    - debug:
+        msg: "{{ inner.rc }}"
+  always:
+    - name: typo
+      comand: echo
+""")
+    rep = _check(ans_dir)
+    codes = rep.codes("error")
+    assert codes.count("var-undefined") == 1 and "task-keyword" in codes
+    assert any("undefined_in_block" in f.message for f in rep.errors)

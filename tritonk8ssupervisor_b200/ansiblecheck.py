@@ -457,6 +457,21 @@ def check_tasks(tasks: Any, path: str, scope: _Scope, play_hosts: str, report: R
             continue
         label = task.get("name") or next((k for k in task if k in MODULES), "task")
         where = "%s task %d (%s)" % (path, idx, label)
+        if "block" in task:
+            # block / rescue / always (2.0+): task lists sharing the block's keywords
+            extra = [k for k in task if k not in TASK_KEYWORDS and k not in ("block", "rescue", "always")
+                     and not k.startswith("with_")]
+            for k in extra:
+                report.error("task-keyword", where, "%r is not valid on a block" % k)
+            reads = expression_names(task.get("when"), "when", where, report)
+            for name in sorted(reads):
+                ok, _ = scope.defined(name, play_hosts)
+                if not ok:
+                    report.error("var-undefined", where, "variable %r is not defined by any vars file, register, loop or fact" % name)
+            for section in ("block", "rescue", "always"):
+                if section in task:
+                    check_tasks(task[section], "%s %s" % (where, section), scope, play_hosts, report)
+            continue
         act = _task_action(task, where, report)
         loop_keys = [k for k in task if k.startswith("with_")] + (["loop"] if "loop" in task else [])
         local: Set[str] = set()
