@@ -64,3 +64,13 @@ def test_tools_as_a_process(tmp_path):
     p = subprocess.run([sys.executable, "-m", "tritonk8ssupervisor_b200.tools", "inventory", str(tmp_path / "w")],
                        capture_output=True, text=True, env=dict(os.environ, PYTHONPATH=rp.PACKAGE_PARENT))
     assert p.returncode == 1 and "not found" in p.stdout
+
+
+def test_launcher_script_is_the_same_program():
+    """bin/tk8s-setup from any cwd == python -m tritonk8ssupervisor_b200 (config 2 replay)."""
+    from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS
+    from tritonk8ssupervisor_b200.conformance.harness import golden_for
+    launcher = os.path.join(rp.PACKAGE_PARENT, "bin", "tk8s-setup")
+    expected, got = rp.replay(golden_for(CONFIGS[1]), argv=[launcher],
+                              extra_env={"TK8S_EXTERNAL_CLOCK": "1", "PYTHONDONTWRITEBYTECODE": "1"})
+    assert expected.diff(got) == []
