@@ -4,10 +4,7 @@
 
 Run once under the replacement and (where available) once under the reference
 script on top of the same simulated tools: identical observations."""
-import os
 import re
-
-import pytest
 
 from tritonk8ssupervisor_b200.conformance import replay as rp
 from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE

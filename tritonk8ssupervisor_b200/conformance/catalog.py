@@ -180,6 +180,16 @@ EDGE: List[Scenario] = [
     Scenario(name="key_dot_matches_any_char", stdin=BLANK8 + YES,
              ssh_files={"akeyxpub": "not a key\n", "id_rsa": "K\n", "id_rsa.pub": "P\n"},
              note="sed 's/.pub$//': the dot is a regex dot, so 'akeyxpub' is asked about as 'akey' (setup.sh:217)"),
+    Scenario(name="key_name_with_ampersand", stdin=BLANK8 + YES, ssh_files={"a&b": "K\n"},
+             keygen={"a&b": "2048 MD5:%s c (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={},
+             note="the key path is spliced into a sed program (setup.sh:133): '&' there means 'the matched text'"),
+    Scenario(name="key_name_with_semicolon", stdin=BLANK8 + YES, ssh_files={"k;": "K\n"},
+             keygen={"k;": "2048 MD5:%s c (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={},
+             note="';' ends the sed replacement; the script's own trailing ';g' becomes the command g and blanks every "
+                  "line of ansible.cfg"),
+    Scenario(name="key_name_breaks_the_sed_program", stdin=BLANK8 + YES, ssh_files={"a;b": "K\n"},
+             keygen={"a;b": "2048 MD5:%s c (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={},
+             note="'a;b': sed rejects the program (unknown option to s), ansible.cfg keeps its old line, tmp.cfg stays behind"),
     Scenario(name="key_no_ssh_dir_entries", stdin="yes\n", ssh_files={}, note="empty ~/.ssh: key not found"),
     Scenario(name="triton_env_fails", stdin="yes\n", fail={"triton-env": 1},
              note="triton env failing is swallowed by eval \"$(...)\"; empty SDC_* then matches the first non-key"),

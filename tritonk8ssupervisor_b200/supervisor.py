@@ -41,6 +41,7 @@ import shutil
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 from . import bashsem as sh
+from . import sedprog
 from . import textops as tx
 from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
 from .tritonenv import TritonEnvError, apply_triton_env
@@ -684,21 +685,26 @@ class Supervisor:
         (setup.sh:133 with ';', setup.sh:511 with '~').  VALUE is spliced into the sed
         program text, so sed's own replacement syntax applies to it."""
         rt = self.rt
-        repl = _sed_replacement(value, delim)
         try:
             rt.write_text(tmp, "")  # the redirection creates/truncates the target first
         except OSError as exc:
             rt.err("%s: line %d: %s: %s\n" % (self.program, lineno, os.path.basename(tmp), exc.strerror))
             return
-        if repl is None:
-            rt.err("sed: -e expression #1, char %d: unknown option to `s'\n" % (len(value) + 40))
-            return
         try:
             text = rt.read_text(cfg)
+            readable = True
         except OSError as exc:
-            rt.err("sed: can't read %s: %s\n" % (shown_src, exc.strerror))
+            text, readable, why = "", False, exc.strerror
+        res = sedprog.run(text, value, delim)
+        if not res.ok:
+            rt.err(res.error)        # a program sed rejects is reported before it opens any input
             return
-        rt.write_text(tmp, tx.sed_sub(text, r"private_key_file = .*$", lambda m: repl(m.group(0)), count=0))
+        if not readable:
+            rt.err("sed: can't read %s: %s\n" % (shown_src, why))
+            return
+        for name, content in res.wfiles.items():     # a `w` flag smuggled in through VALUE writes next to the input
+            rt.write_text(os.path.join(os.path.dirname(tmp), name), content)
+        rt.write_text(tmp, res.output)
         os.replace(rt.path(tmp), rt.path(cfg))
 
     # ------------------------------------------------------------------
@@ -834,36 +840,3 @@ def _rm_rf(path: str) -> None:
             os.remove(path)
         except OSError:
             pass
-
-
-def _sed_replacement(value: str, delim: str) -> Optional[Callable[[str], str]]:
-    """Interpret VALUE as the replacement half of a sed ``s`` command whose
-    delimiter is ``delim``.  Returns a function matched-text -> replacement, or
-    None when VALUE makes the sed program invalid (unescaped delimiter/newline)."""
-    parts: List[Tuple[str, str]] = []
-    i, n = 0, len(value)
-    while i < n:
-        c = value[i]
-        if c == "\\" and i + 1 < n:
-            d = value[i + 1]
-            i += 2
-            if d == "n":
-                parts.append(("lit", "\n"))
-            elif d in "123456789":
-                return None  # reference to a group the expression does not have
-            elif d == "0":
-                parts.append(("match", ""))
-            else:
-                parts.append(("lit", d))
-            continue
-        if c == delim or c == "\n":
-            return None
-        if c == "&":
-            parts.append(("match", ""))
-        else:
-            parts.append(("lit", c))
-        i += 1
-
-    def render(matched: str) -> str:
-        return "private_key_file = " + "".join(matched if k == "match" else t for k, t in parts)
-    return render
