@@ -558,7 +558,13 @@ def check_playbook(playbook: str, inventory: Optional[Inventory] = None) -> Repo
         if "hosts" not in play:
             report.error("play-shape", where, "play has no 'hosts'")
             continue
-        hosts = play["hosts"] if isinstance(play["hosts"], str) else ":".join(map(str, play["hosts"] or []))
+        if isinstance(play["hosts"], str):
+            hosts = play["hosts"]
+        elif isinstance(play["hosts"], list) and all(isinstance(h, str) for h in play["hosts"]):
+            hosts = ":".join(play["hosts"])
+        else:
+            report.error("play-shape", where, "hosts must be a pattern string or a list of them")
+            continue
         if inventory is not None:
             for g in _hosts_groups(play["hosts"]):
                 if g not in ("all", "*", "localhost") and g not in inventory.groups and g not in inventory.hostvars:
@@ -574,7 +580,13 @@ def check_playbook(playbook: str, inventory: Optional[Inventory] = None) -> Repo
             if k in MAGIC_VARS:
                 report.warn("magic-shadowed", where, "play var %r cannot override the magic variable of that name" % k)
             play_scope_vars.add(k)
-        for entry in play.get("vars_files") or []:
+        vars_files = play.get("vars_files") or []
+        if isinstance(vars_files, str):
+            vars_files = [vars_files]
+        elif not isinstance(vars_files, list):
+            report.error("play-shape", where, "vars_files must be a list of paths")
+            vars_files = []
+        for entry in vars_files:
             paths = entry if isinstance(entry, list) else [entry]
             loaded = False
             for raw in paths:
