@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, ROOT)
 
-from oracle.reference_runner import REFERENCE_ARGV, find_reference, reference_sha256  # noqa: E402
+from oracle.reference_runner import find_reference, reference_sha256  # noqa: E402
 from tritonk8ssupervisor_b200.conformance.catalog import ALL  # noqa: E402
 from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox  # noqa: E402
 
@@ -31,11 +31,11 @@ def make(scenario, ref_root):
         listing = sorted(sbx.snapshot().keys())
         # files the scenario itself planted are not part of the static tree
         listing = [p for p in listing if p not in scenario.pre_files]
-        obs = sbx.run(REFERENCE_ARGV)
+        obs = sbx.run(scenario.reference_argv())
     return {
         "generated_by": "oracle/make_golden.py",
         "reference": {"repo": "cheapRoc/tritonK8ssupervisor", "setup_sh_sha256": reference_sha256(ref_root),
-                      "argv": REFERENCE_ARGV},
+                      "argv": scenario.reference_argv()},
         "scenario": scenario.to_json(),
         "workspace_listing": listing,
         "inputs": inputs,

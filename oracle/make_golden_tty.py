@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, ROOT)
 
-from oracle.reference_runner import REFERENCE_ARGV, find_reference, reference_sha256  # noqa: E402
+from oracle.reference_runner import find_reference, reference_sha256  # noqa: E402
 from tritonk8ssupervisor_b200.conformance.catalog import TTY_CASES  # noqa: E402
 from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox, run_on_pty  # noqa: E402
 
@@ -31,7 +31,7 @@ def main() -> int:
         with Sandbox(ref, sc) as sbx:
             inputs = sbx.read_inputs()
             listing = sorted(p for p in sbx.snapshot() if p not in sc.pre_files)
-            transcript = run_on_pty(sbx, REFERENCE_ARGV, answers)
+            transcript = run_on_pty(sbx, sc.reference_argv(), answers)
         doc = {"generated_by": "oracle/make_golden_tty.py", "reference": {"setup_sh_sha256": reference_sha256(ref)},
                "scenario": sc.to_json(), "answers": answers, "inputs": inputs, "workspace_listing": listing,
                "transcript": transcript}

@@ -16,8 +16,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 STAGED = os.path.join(HERE, "_ref", "reference")
 CANDIDATES = ("/root/reference", STAGED)
 
-#: how the reference is invoked inside the sandbox (cwd = workspace root)
-REFERENCE_ARGV = ["bash", "setup.sh"]
+#: how the reference is invoked inside the sandbox (cwd = workspace root) unless the
+#: scenario says otherwise: the documented way, README.md:105 `$ ./setup.sh`
+REFERENCE_ARGV = ["./setup.sh"]
 
 
 def find_reference() -> Optional[str]:
@@ -42,4 +43,4 @@ def run_reference(scenario: Scenario, root: Optional[str] = None,
     if root is None:
         raise FileNotFoundError("no reference tree (looked in %s)" % (CANDIDATES,))
     with Sandbox(root, scenario, input_overrides) as sbx:
-        return sbx.run(REFERENCE_ARGV)
+        return sbx.run(scenario.reference_argv())

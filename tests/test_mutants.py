@@ -7,7 +7,7 @@ import os
 
 import pytest
 
-from tritonk8ssupervisor_b200 import bashsem, supervisor, textops
+from tritonk8ssupervisor_b200 import basharith, bashsem, runtime, supervisor, textops
 from tritonk8ssupervisor_b200.conformance import replay as rp
 
 GOLDENS = {os.path.basename(p)[:-5]: rp.load_golden(p) for p in rp.list_goldens()}
@@ -60,7 +60,11 @@ MUTANTS = [
      lambda t: t.split("\n")[0] + "\n" if t else "", {"stale_ip_files_are_appended_to"}),
     ("word count instead of exact container count: wc -w counts lines", textops, "wc_w", lambda t: t.count("\n") + 5,
      {"wait_stuck_dashboard_killed", "wait_two_containers_but_other_error"}),
-    ("arithmetic does not wrap at 2**64", supervisor, "_to_int64", lambda t: int(t) if t.isdigit() else 0, {"pkg_huge_index"}),
+    ("arithmetic does not wrap at 2**64", basharith, "wrap", lambda v: v, {"pkg_huge_index"}),
+    ("the result of ~ is pathname-expanded like the rest of the word", bashsem, "quote_for_glob", lambda t: t, {"home_glob_chars"}),
+    ("HOME unset means the empty string", runtime.Runtime, "passwd_home", lambda self: "", {"home_unset"}),
+    ("the previous-run guard sees dangling links ([ -L ] instead of [ -e ])", runtime.Runtime, "exists",
+     lambda self, rel: os.path.lexists(self.path(rel)), {"ws_rancher_tf_dangling_symlink"}),
 ]
 
 
@@ -127,7 +131,80 @@ def _clean_dotfiles_too(orig):
     return _clean
 
 
+def _arith_digits_only(orig):
+    def arith_eval(self, expr, lineno, command, last_status=0):
+        if lineno == 64 and not expr[:-len(" % 15")].isdigit():
+            return 1                     # "not a number: keep sleeping" -- what round 1 did
+        return orig(self, expr, lineno, command, last_status)
+    return arith_eval
+
+
+def _arith_error_is_zero(orig):
+    def arith_eval(self, expr, lineno, command, last_status=0):
+        val = orig(self, expr, lineno, command, last_status)
+        return 0 if val is None and command == "[[" else val
+    return arith_eval
+
+
+def _for_error_exits(orig):
+    def arith_eval(self, expr, lineno, command, last_status=0):
+        val = orig(self, expr, lineno, command, last_status)
+        if val is None and lineno == 148:
+            raise supervisor.ScriptExit(1)
+        return val
+    return arith_eval
+
+
+def _mv_writes_through_links(src, dst):
+    with open(src, "rb") as fh:
+        data = fh.read()
+    with open(dst, "wb") as fh:          # follows a symbolic link at dst; mv replaces it
+        fh.write(data)
+    os.remove(src)
+
+
+_real_rm_rf = supervisor._rm_rf
+
+
+def _rm_rf_following(path):
+    _real_rm_rf(os.path.realpath(path))
+    _real_rm_rf(path)
+
+
+def _read_in_blocks(self, prompt):
+    """stdin slurped into a private buffer on the first read: children that
+    inherit stdin then find it empty."""
+    if not hasattr(self, "_private"):
+        self._private, self._ppos = self._stdin[self._pos:], 0
+        self._pos = len(self._stdin)
+
+    def nb():
+        if self._ppos >= len(self._private):
+            return None
+        self._ppos += 1
+        return self._private[self._ppos - 1]
+    return bashsem.read_builtin(nb)
+
+
 MUTANTS_2 = [
+    ("a clock reading that is not a number is skipped", supervisor.Supervisor, "arith_eval",
+     _arith_digits_only(supervisor.Supervisor.arith_eval),
+     {"wait_clock_word", "wait_clock_negative", "wait_clock_empty", "wait_clock_two_words",
+      "wait_clock_bases_and_operators", "wait_clock_names_script_variables", "wait_clock_subscripts", "wait_clock_subscript_error"}),
+    ("an operand [[ -gt ]] cannot evaluate counts as 0", supervisor.Supervisor, "arith_eval",
+     _arith_error_is_zero(supervisor.Supervisor.arith_eval), {"pkg_arith_operands"}),
+    ("an arithmetic error in the node loop ends the run", supervisor.Supervisor, "arith_eval",
+     _for_error_exits(supervisor.Supervisor.arith_eval), {"count_invalid_via_name"}),
+    ("mv writes through a symbolic link", supervisor.os, "replace", _mv_writes_through_links, {"ws_ansible_cfg_is_a_symlink"}),
+    ("stdin read in blocks", __import__("tritonk8ssupervisor_b200.conformance.modeltools", fromlist=["x"]).ModelRuntime, "read",
+     _read_in_blocks, {"stdin_taken_by_triton", "stdin_taken_by_terraform", "stdin_taken_by_ssh_in_wait_loop",
+                       "stdin_taken_by_destroy_on_clean"}),
+    ("rm -rf follows symbolic links", supervisor, "_rm_rf", lambda path: _rm_rf_following(path), {"ws_clean_with_symlinks"}),
+    ("leading zeros are decimal", basharith.Evaluator, "_strlong", lambda self, num: int(num) if num.isdigit() else 0,
+     {"wait_clock_leading_zero", "pkg_arith_octal_operand"}),
+    ("diagnostics always labelled setup.sh", __import__("tritonk8ssupervisor_b200.conformance.scenario", fromlist=["x"]).Scenario,
+     "program_label", property(lambda self: "setup.sh"), {"text_embedded_newline", "missing_terraform", "wait_clock_empty"}),
+
     ("menu rows sorted before the blank->'=' rewrite", supervisor.Supervisor, "_menu_rows", _menu_rows_sorted_raw,
      {"net_prefix_collision", "pkg_prefix_collision"}),
     (".pub stripped with a literal dot", textops, "sed_sub", _sed_literal_dot(textops.sed_sub), {"key_dot_matches_any_char"}),

@@ -103,7 +103,10 @@ _PS_LINES = st.lists(st.sampled_from([
     "   ", "CONTAINER ID  IMAGE  NAMES"]), max_size=4).map(lambda ls: "".join(l + "\n" for l in ls))
 _BODIES = st.sampled_from(["", "503 Service Unavailable\n", "service unavailable", "502 Bad Gateway\n", "<html>starting</html>\n",
                            "* ? [a]\n", "-n kubernetes\n", "-e x\\nkubernetes\n", "KuBeRnEtEs", "two\nlines\n"])
-_EPOCHS = st.sampled_from(["1500000000", "1500000001", "1500000015", "1500000029", "1500000030", "0"])
+_EPOCHS = st.sampled_from(["1500000000", "1500000001", "1500000015", "1500000029", "1500000030", "0",
+                           # setup.sh:64 evaluates the reading as an arithmetic expression
+                           "abc", "", "08", "-15", "-16", "15 30", "0x1e", "0x1f", "16#f", "1.5", "i", "n++", "1/0", "(30", "yn",
+                           "99999999999999999999", "DASHBOARD_CONTAINER_COUNT+1", "node", "i[0]", "i[1]", "2**4-1"])
 
 
 @settings(max_examples=25, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))

@@ -95,6 +95,28 @@ def test_second_run_is_idempotent(tmp_path, label, src):
 
 
 @pytest.mark.parametrize("label,src", _sources(), ids=[s[0] for s in _sources()])
+def test_failed_join_is_retried_by_a_second_run(tmp_path, label, src):
+    """The agent's bootstrap container exits without starting `rancher-agent`
+    (bad token, server not ready).  The guard on every node task is the substring
+    'rancher-agent' in `docker ps -a` (rancherhost/tasks/main.yml:9-34), so a
+    second run must still find it open and ask for tokens again -- which it only
+    does if the bootstrap container's own name does not contain that substring."""
+    d = _tree(tmp_path, src)
+    with ranchermock.RancherMock() as mock:
+        first = _run(d, mock, agent_bootstrap_fails=True)
+        assert first.failed_hosts == {}
+        for h in ("10.0.1.1", "10.0.1.2"):
+            assert "rancher-agent" not in first.hosts[h].docker_ps()
+        n_req = len(mock.requests)
+        second = _run(d, mock, hosts=first.hosts)
+        assert second.failed_hosts == {}
+        retried = [r for r in mock.wire_log()[n_req:] if r.startswith("POST /v1/registrationtokens")]
+        assert len(retried) == 2
+        for h in ("10.0.1.1", "10.0.1.2"):
+            assert "rancher-agent" in second.hosts[h].docker_ps()
+
+
+@pytest.mark.parametrize("label,src", _sources(), ids=[s[0] for s in _sources()])
 def test_project_creation_rejected(tmp_path, label, src):
     """Rancher answers 500 to POST /v2-beta/projects: the task fails on status_code 201,
     run_once takes every host of the play down, nodes never ask for tokens."""

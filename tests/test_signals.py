@@ -1,0 +1,92 @@
+"""Ctrl-C while a provisioning tool runs, and a reader that goes away.
+
+bash does not act on SIGINT while a foreground child is running: it waits for
+the child, and then dies of the signal itself only if the child did.  A tool
+that traps the signal to save its state (terraform does) therefore always gets
+to finish before the operator has the prompt back.  Compared live with the
+reference where a reference tree is available."""
+import os
+import signal
+import subprocess
+import time
+
+import pytest
+
+from tritonk8ssupervisor_b200.conformance import replay as rp
+from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS
+from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE
+from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox
+
+#: terraform stand-ins: apply announces itself, then sleeps until interrupted
+_TRAPS_AND_SAVES = """#!/bin/sh
+[ "$1" = apply ] || exit 0
+trap 'sleep 0.5; echo "state saved" >> saved.txt; echo 10.0.0.1 >> masters.ip; echo 10.0.1.1 >> hosts.ip; exit %d' INT
+touch started
+while :; do /bin/sleep 0.05; done
+"""
+_DIES = """#!/bin/sh
+[ "$1" = apply ] || exit 0
+touch started
+exec /bin/sleep 30
+"""
+
+
+def _interrupt_during_apply(argv, env_extra, workspace_src, stub):
+    with Sandbox(workspace_src, CONFIGS[0]) as sbx:
+        tf = os.path.join(sbx.bin, "terraform")
+        with open(tf, "w") as fh:
+            fh.write(stub)
+        os.chmod(tf, 0o755)
+        proc = subprocess.Popen(list(argv), cwd=sbx.workspace, stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                                env=sbx.env(env_extra), start_new_session=True)
+        proc.stdin.write(CONFIGS[0].stdin.encode())
+        proc.stdin.flush()
+        started = os.path.join(sbx.workspace, "terraform", "started")
+        deadline = time.time() + 30
+        while not os.path.exists(started) and time.time() < deadline:
+            time.sleep(0.02)
+        assert os.path.exists(started), proc.stderr.read()
+        os.killpg(proc.pid, signal.SIGINT)              # what the terminal does on Ctrl-C
+        out, err = proc.communicate(timeout=30)
+        saved = os.path.exists(os.path.join(sbx.workspace, "terraform", "saved.txt"))
+        return {"status": proc.returncode, "saved_before_exit": saved, "tail": out.decode().splitlines()[-1:],
+                "ansible_ran": b"PLAY RECAP" in out}
+
+
+CASES = [("child traps SIGINT and fails", _TRAPS_AND_SAVES % 1, {"status": 1, "saved_before_exit": True, "ansible_ran": False}),
+         ("child traps SIGINT and succeeds", _TRAPS_AND_SAVES % 0, {"status": 0, "saved_before_exit": True, "ansible_ran": True}),
+         ("child dies of SIGINT", _DIES, {"status": -signal.SIGINT, "saved_before_exit": False, "ansible_ran": False})]
+
+
+@pytest.mark.parametrize("label,stub,want", CASES, ids=[c[0] for c in CASES])
+def test_sigint_during_terraform_apply(label, stub, want):
+    got = _interrupt_during_apply(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, WORKSPACE_TEMPLATE, stub)
+    assert {k: got[k] for k in want} == want
+
+
+@pytest.mark.parametrize("label,stub,want", CASES, ids=[c[0] for c in CASES])
+def test_sigint_same_as_reference(ref_root, label, stub, want):
+    theirs = _interrupt_during_apply(["./setup.sh"], None, ref_root, stub)
+    mine = _interrupt_during_apply(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root, stub)
+    assert mine == theirs
+
+
+def _reader_goes_away(argv, env_extra, workspace_src):
+    """stdout is a pipe whose reader exits after the first line."""
+    with Sandbox(workspace_src, CONFIGS[0]) as sbx:
+        proc = subprocess.Popen(list(argv), cwd=sbx.workspace, stdin=subprocess.PIPE, stdout=subprocess.PIPE,
+                                stderr=subprocess.DEVNULL, env=sbx.env(env_extra))
+        proc.stdout.readline()
+        proc.stdout.close()
+        proc.stdin.write(CONFIGS[0].stdin.encode())
+        proc.stdin.close()
+        return proc.wait(timeout=30), os.path.exists(os.path.join(sbx.workspace, "terraform", "rancher.tf"))
+
+
+def test_sigpipe_kills_like_a_shell_script():
+    status, wrote = _reader_goes_away(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, WORKSPACE_TEMPLATE)
+    assert status == -signal.SIGPIPE and not wrote
+
+
+def test_sigpipe_same_as_reference(ref_root):
+    assert _reader_goes_away(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root) == _reader_goes_away(["./setup.sh"], None, ref_root)

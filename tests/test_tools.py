@@ -72,5 +72,5 @@ def test_launcher_script_is_the_same_program():
     from tritonk8ssupervisor_b200.conformance.harness import golden_for
     launcher = os.path.join(rp.PACKAGE_PARENT, "bin", "tk8s-setup")
     expected, got = rp.replay(golden_for(CONFIGS[1]), argv=[launcher],
-                              extra_env={"TK8S_EXTERNAL_CLOCK": "1", "PYTHONDONTWRITEBYTECODE": "1"})
+                              extra_env={"PYTHONDONTWRITEBYTECODE": "1", "TK8S_PROGRAM": "<PROGRAM>"})
     assert expected.diff(got) == []

@@ -8,8 +8,8 @@ import pytest
 from tritonk8ssupervisor_b200.conformance.scenario import triton_env_text
 from tritonk8ssupervisor_b200.tritonenv import TritonEnvError, apply_triton_env
 
-NAMES = ["SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID", "SDC_USER", "SDC_TESTING", "TRITON_PROFILE", "DOCKER_HOST", "PLAIN", "EMPTY"]
-START = {"SDC_USER": "old-user", "SDC_TESTING": "1", "PLAIN": "exported-before"}
+NAMES = ["SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID", "SDC_USER", "SDC_TESTING", "TRITON_PROFILE", "DOCKER_HOST", "PLAIN", "EMPTY", "A", "B"]
+START = {"SDC_USER": "old-user", "SDC_TESTING": "1", "PLAIN": "exported-before", "HOME": "/home/op er*", "GLOBBY": "a  b * c"}
 
 
 def bash_eval(text):
@@ -45,6 +45,20 @@ ACCEPTED = [
     'export SDC_URL=back\\ slash\\"x\n',
     "export SDC_ACCOUNT\n",
     "",
+    # parameter references execute nothing: expanded as bash expands an assignment
+    # (no field splitting, no pathname expansion), earlier assignments visible to later ones
+    'export SDC_URL="https://$HOME/x"\n',
+    'export SDC_URL="${HOME}y$SDC_USER" SDC_ACCOUNT=$SDC_USER$UNSET_THING.\n',
+    "export SDC_URL=$GLOBBY\nexport SDC_ACCOUNT=\"$GLOBBY\"\nPLAIN=$GLOBBY\n",
+    'A=one\nB="$A two"\nexport SDC_URL="$B $A"\nunset A\nexport SDC_ACCOUNT="[$A]"\n',
+    'export SDC_URL="cost: 5$ and $ and $. and a$"\nexport SDC_ACCOUNT=x$\n',
+    'export SDC_URL="\\$HOME" SDC_ACCOUNT=\\$HOME SDC_KEY_ID=\'$HOME\'\n',
+    # tilde: at the start of an assigned value and after an unquoted colon, nowhere else
+    "export SDC_URL=~/x\nexport SDC_ACCOUNT=~\nexport SDC_KEY_ID=a~/b\n",
+    "export SDC_URL=~/a:~/b:c~:~\nPLAIN=~/p\n",
+    'export SDC_URL="~/quoted" SDC_ACCOUNT=\\~/escaped SDC_KEY_ID=~"/half"\n',
+    "export SDC_URL=~root/x SDC_ACCOUNT=~nosuchuser_zz/x SDC_KEY_ID=~ro\"ot\"/x\n",
+    "export SDC_URL=x=~/y\nexport SDC_ACCOUNT=$HOME:~\n",
 ]
 
 
@@ -54,9 +68,12 @@ def test_same_variables_as_bash_eval(text):
 
 
 @pytest.mark.parametrize("text", [
-    'export SDC_URL="$(curl evil)"\n', "export SDC_URL=`id`\n", 'export SDC_URL="$HOME/x"\n', "rm -rf /\n",
-    "export SDC_URL=a | tee x\n", "export 1BAD=x\n", "export SDC_URL=$HOME\n", "echo hi > /tmp/x\n", "export A=(1 2)\n",
+    'export SDC_URL="$(curl evil)"\n', "export SDC_URL=`id`\n", 'export SDC_URL="`id`"\n', "rm -rf /\n",
+    "export SDC_URL=a | tee x\n", "export 1BAD=x\n", "export SDC_URL=$(id)\n", "echo hi > /tmp/x\n", "export A=(1 2)\n",
     'export SDC_URL="unterminated\n', "export SDC_URL='unterminated\n", "eval foo\n", "A=1 B=2\n",
+    'export SDC_URL="$((1+1))"\n', 'export SDC_URL="${HOME:-x}"\n', 'export SDC_URL="${HOME"\n', "export SDC_URL=$1\n",
+    'export SDC_URL="$?"\n', "export SDC_URL=$'ansi'\n", "unset $HOME\n", "$HOME\n", "export $HOME=x\n", "export SDC_URL=$_\n",
+    "export SDC_URL=~+/x\n", "export SDC_URL=${!HOME}\n", "export SDC_URL=$$\n",
 ])
 def test_everything_else_is_refused(text):
     with pytest.raises(TritonEnvError):

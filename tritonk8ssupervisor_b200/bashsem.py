@@ -38,6 +38,23 @@ def c_sort_key(s: str) -> bytes:
     return to_bytes(s)
 
 
+# Quoted text inside a word that is otherwise subject to pathname expansion
+# (the result of tilde expansion, setup.sh:216-217: bash never globs or splits
+# it): its pattern characters are carried as private-use code points so the
+# globbing code sees ordinary characters, and mapped back on the way out.
+_QUOTED_BASE = 0xE000
+_QUOTABLE = "*?[]\\"
+
+
+def quote_for_glob(text: str) -> str:
+    """Mark ``text`` as quoted: none of its characters is a pattern character."""
+    return "".join(chr(_QUOTED_BASE + ord(c)) if c in _QUOTABLE else c for c in text)
+
+
+def _unquote(text: str) -> str:
+    return "".join(chr(ord(c) - _QUOTED_BASE) if _QUOTED_BASE <= ord(c) < _QUOTED_BASE + 128 else c for c in text)
+
+
 # ---------------------------------------------------------------------------
 # read  (bash builtin, no -r, one variable, default IFS)
 # ---------------------------------------------------------------------------
@@ -224,7 +241,7 @@ def glob_to_regex(pat: str, pathname: bool = True) -> str:
             else:
                 out.append(re.escape("\\"))
         else:
-            out.append(re.escape(c))
+            out.append(re.escape(_unquote(c)))
     return "(?s:" + "".join(out) + r")\Z"
 
 
@@ -253,7 +270,7 @@ def _unescape_glob(s: str) -> str:
 def glob_word(word: str, cwd: str) -> List[str]:
     """Pathname expansion of one field; the word itself when nothing matches."""
     if not _has_glob_chars(word):
-        return [word]
+        return [_unquote(word)]
     absolute = word.startswith("/")
     parts = word.split("/")
     # candidates are (display path, filesystem path)
@@ -285,7 +302,7 @@ def glob_word(word: str, cwd: str) -> List[str]:
                         if last or os.path.isdir(p):
                             nxt.append((_join_disp(disp, name), p))
         else:
-            name = _unescape_glob(comp)
+            name = _unquote(_unescape_glob(comp))
             for disp, fs in cands:
                 p = os.path.join(fs, name)
                 if os.path.lexists(p) and (last or os.path.isdir(p)):
@@ -294,7 +311,7 @@ def glob_word(word: str, cwd: str) -> List[str]:
         if not cands:
             break
     if not cands:
-        return [word]
+        return [_unquote(word)]
     return sorted((d for d, _ in cands), key=c_sort_key)
 
 
@@ -316,6 +333,7 @@ def expand_word(segments: Sequence[Tuple[str, bool]], cwd: str) -> List[str]:
     """Expand one shell word made of literal text and unquoted substitutions.
 
     ``segments`` is a list of (text, is_unquoted_expansion).  Literal text
+    (pass it through :func:`quote_for_glob` when the shell treats it as quoted)
     glues to the neighbouring fields the way it does in the shell:
     ``http://$(cat f):8080`` with a two-line ``f`` gives two words
     (setup.sh:66)."""

@@ -9,6 +9,7 @@ a reference test.
 """
 from __future__ import annotations
 
+import dataclasses
 from typing import Dict, List
 
 from .scenario import DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario, triton_table
@@ -275,6 +276,121 @@ EDGE: List[Scenario] = [
              note="ssh-keygen -R failing ends the clean half-way (errexit)"),
     Scenario(name="clean_other_arg_ignored", args=["--clean"], stdin=BLANK8 + YES, note="only -c means clean; anything else is a normal run"),
 ]
+
+_STARTING = "<html>starting</html>\n"
+_CFG = "[defaults]\nhost_key_checking = False\nprivate_key_file =\n"
+
+EDGE += [
+    # --- the clock reading is an arithmetic expression (setup.sh:64) -------------
+    Scenario(name="wait_clock_word", stdin=BLANK8 + YES, date_seq=["abc", "1500000001"], curl_seq=[_STARTING],
+             note="a bare word is an unset variable = 0: `! ((abc % 15))` fires on the first reading"),
+    Scenario(name="wait_clock_negative", stdin=BLANK8 + YES, date_seq=["-15", "-14", "- 30"], curl_seq=[_STARTING],
+             note="-15 and `- 30` are divisible by 15, -14 is not"),
+    Scenario(name="wait_clock_leading_zero", stdin=BLANK8 + YES, date_seq=["08", "010", "017"], curl_seq=[_STARTING],
+             note="08: 'value too great for base', status 1, `!` makes it fire; 010 is octal 8 (no poll), 017 is 15 (poll)"),
+    Scenario(name="wait_clock_empty", stdin=BLANK8 + YES, date_seq=["", " "], curl_seq=[_STARTING],
+             note="no reading at all: `(( % 15))` is a syntax error (operand expected) and the poll fires"),
+    Scenario(name="wait_clock_two_words", stdin=BLANK8 + YES, date_seq=["15 30", "1500000000 x"], curl_seq=[_STARTING],
+             note="two words: 'syntax error in expression', fires"),
+    Scenario(name="wait_clock_bases_and_operators", stdin=BLANK8 + YES,
+             date_seq=["0x1e", "0x1f", "16#1E", "2#102", "65#1", "1/0", "14+1", "2**4-1", "1.5", "99999999999999999999", "7 ?", "(15"],
+             curl_seq=[_STARTING] * 9,
+             note="hex/base# literals, operators, division by zero, 64-bit wrap-around, and bash's wording for each error"),
+    Scenario(name="wait_clock_names_script_variables", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             date_seq=["KUBERNETES_NUMBER_OF_NODES", "i", "i*5", "yn", "master", "RANCHER_MASTER_HOSTNAME", "HOST_PACKAGE",
+                       "LINENO", "DASHBOARD_CONTAINER_COUNT", "t=45", "t", "t++ - 31", "t"],
+             curl_seq=[_STARTING] * 6,
+             note="an identifier is looked up among the script's own variables (i is 3 after the node loop, yn is 'yes' = "
+                  "unset variable yes, the quoted hostname is an error) and assignments persist between readings"),
+    Scenario(name="wait_clock_subscript_error", stdin=BLANK8 + YES, date_seq=["i[1+]"],
+             note="an error inside an array subscript makes bash drop the whole top-level command: main ends, status 1"),
+    Scenario(name="wait_clock_subscripts", stdin=BLANK8 + YES, date_seq=["i[0]", "i[1]", "i[-1]", "i[@]", "i[0"],
+             curl_seq=[_STARTING] * 3,
+             note="a scalar is element 0 of itself; other elements are unset; a negative or unterminated subscript is reported"),
+    # --- text from ./config reaches the node loop's test expression (setup.sh:148) ---
+    Scenario(name="count_expression_via_description",
+             stdin=_answers("", "-e x\\\\nKUBERNETES_NUMBER_OF_NODES=1+1\\\\nPAD=", "", "", "", "", "", "", "yes"),
+             note="an echo -e newline smuggles a second KUBERNETES_NUMBER_OF_NODES line into ./config; exportVars exports "
+                  "it and `i <= 1+1` provisions two workers"),
+    Scenario(name="count_invalid_via_name",
+             stdin=_answers("-e a\\\\nKUBERNETES_NUMBER_OF_NODES=2", "", "", "", "", "", "", "", "yes"),
+             note="same route, but the closing quote of the name lands in the count: `i <= 2\"` is an arithmetic error, "
+                  "the for command fails and errexit ends the run after the master block"),
+    # --- a word bash cannot evaluate reaches [[ -gt ]] (setup.sh:431) ----------------
+    Scenario(name="pkg_arith_operands",
+             stdin=_answers("", "", "", "", "", "", "", "-e \\\\055e 3\\\\\\\\nzz", "-e \\\\055e 4\\\\\\\\n077", "-e \\\\055e 5\\\\\\\\n1.5", "yes"),
+             note="echo -e '\\055e ...' prints a leading -e, so the *next* echo makes two lines: grep passes on the first, "
+                  "and the second word is an operand of [[ -gt ]] (setup.sh:431): an unset name is 0 (below 1), 077 is octal 63 "
+                  "(above the count of 18), and 1.5 is an arithmetic error, which makes both tests false: in range"),
+    Scenario(name="pkg_arith_octal_operand",
+             stdin=_answers("", "", "", "", "", "", "", "-e \\\\055e 6\\\\\\\\n022", "yes"),
+             note="022 is octal 18, just inside 1..18 (decimal 22 would not be)"),
+    # --- tilde expansion (setup.sh:216-217,504) ---------------------------------------
+    Scenario(name="home_glob_chars", stdin=BLANK8 + YES, home_name="h*me", home_decoys=["home"],
+             note="HOME=/.../h*me beside /.../home: the result of ~ is never globbed, ssh-keygen gets one path"),
+    Scenario(name="home_with_space", stdin=BLANK8 + YES, home_name="my home",
+             note="... and never split"),
+    Scenario(name="home_unset", stdin="yes\n", unset_env=["HOME"],
+             note="HOME unset: ~ is the password-database home of the user, not the empty string"),
+    Scenario(name="home_empty", stdin="yes\n", env={"HOME": ""},
+             note="HOME set but empty: ~ expands to nothing, `ls /.ssh`"),
+    Scenario(name="home_clean_known_hosts_glob", args=["-c"], stdin="yes\n", pre_files=_RAN_FILES, known_hosts="h\n",
+             home_name="h[o]me", home_decoys=["home"],
+             note="[[ -e ~/.ssh/known_hosts ]] with pattern characters in HOME: still a literal path"),
+    # --- `triton env` output that refers to variables (eval at setup.sh:210) ------------
+    Scenario(name="triton_env_refers_to_variables", stdin=BLANK8 + YES,
+             triton_env='PREFIX=https://$HOME\nexport SDC_URL="${PREFIX}/x"\nexport SDC_ACCOUNT=$UNSET_ONE"acct"\n'
+                        'export SDC_KEY_ID="%s"\nexport TRITON_PROFILE=~/profile:~\n' % DEFAULT_KEY_ID,
+             note="$NAME, ${NAME} and ~ in assignments execute nothing and are expanded as bash's eval expands them"),
+    # --- children that read the stdin they inherit ------------------------------------
+    Scenario(name="stdin_taken_by_ssh_keygen", stdin="eaten by ssh-keygen\n" + BLANK8 + YES, stdin_eaters={"ssh-keygen--E": 1},
+             note="stdin is read a byte at a time, so a child sees exactly what is left: here the first line"),
+    Scenario(name="stdin_taken_by_triton", stdin=_answers("menu", "resolver", "", "", "", "", "", "", "", "", "yes") + "tail\n",
+             stdin_eaters={"triton-networks": 1},
+             note="`triton networks` heads six pipelines; each call takes the line the next prompt would have read"),
+    Scenario(name="stdin_taken_by_terraform", stdin=BLANK8 + YES + "approve\nsecond\nthird\n", stdin_eaters={"terraform-apply": 2},
+             note="terraform asking for approval reads what follows the confirmation"),
+    Scenario(name="stdin_taken_by_ssh_in_wait_loop", stdin=BLANK8 + YES + "one\ntwo\nthree\n", stdin_eaters={"ssh--o": 1},
+             curl_seq=[_STARTING], note="ssh without -n in the wait loop drains the script's stdin"),
+    Scenario(name="stdin_taken_by_destroy_on_clean", args=["-c"], stdin="yes\nfor terraform\n", pre_files=_RAN_FILES,
+             stdin_eaters={"terraform-destroy": 1}, note="clean: terraform destroy inherits stdin too"),
+    # --- odd workspaces: symbolic links ---------------------------------------------------
+    Scenario(name="ws_rancher_tf_dangling_symlink", stdin=BLANK8 + YES, pre_symlinks={"terraform/rancher.tf": "elsewhere.tf"},
+             note="the previous-run guard is [ -e ] (setup.sh:14), false for a dangling link: the run proceeds and writes through it"),
+    Scenario(name="ws_hosts_symlink_to_dev_null", stdin=BLANK8 + YES, pre_symlinks={"ansible/hosts": "/dev/null"},
+             note="rm -f removes the link, the inventory is a regular file afterwards"),
+    Scenario(name="ws_ansible_cfg_is_a_symlink", stdin=BLANK8 + YES, pre_remove=["ansible/ansible.cfg"],
+             pre_files={"ansible/real.cfg": _CFG}, pre_symlinks={"ansible/ansible.cfg": "real.cfg"},
+             note="sed reads through the link, mv replaces the link itself (setup.sh:133): real.cfg is untouched"),
+    Scenario(name="ws_clean_with_symlinks", args=["-c"], stdin="yes\n", pre_files={"ansible/real.cfg": _CFG, "elsewhere/keep": "k\n"},
+             pre_remove=["ansible/ansible.cfg"],
+             pre_symlinks={"ansible/ansible.cfg": "real.cfg", "terraform/rancher.tf": "../elsewhere/keep", "tmp/link": "../elsewhere",
+                           "terraform/.terraform": "../elsewhere"},
+             note="rm -rf removes links, never what they point to"),
+    # --- bytes ------------------------------------------------------------------------------
+    Scenario(name="text_70kb_line", stdin=_answers("x" * 70000, "", "", "", "", "", "", "", "yes"),
+             note="a 70 KB answer: no line-length limit anywhere on the path"),
+    Scenario(name="text_raw_bytes", stdin="\udcff\udcfe\x01\x1b[31m\x7f\n" + "\udc80 \x02\t\x03\n" + "\n" * 6 + YES,
+             note="0xFF/0xFE, C0 controls and ESC are data; 0x01 and 0x7f are bash's internal quoting bytes"),
+    # --- the operator's environment -----------------------------------------------------------
+    Scenario(name="env_lang_utf8_no_lc_all", stdin=_answers("caf\u00e9 \u2615", "", "", "", "", "2,1", "", "", "yes"),
+             env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"], note="LANG=C.UTF-8 with LC_ALL unset: same bytes, same order"),
+    Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
+             note="PATH without /usr/bin"),
+    Scenario(name="env_own_switches_do_not_leak", stdin=BLANK8 + YES,
+             env={"TK8S_PROGRAM_": "1", "KUBERNETES_TK8S": "kept"},
+             note="variables that merely look like the replacement's own switches pass through to terraform/ansible"),
+]
+
+#: scenarios whose stderr carries bash's own diagnostics: recorded under both ways
+#: of starting the script, since bash labels them with the name it was given
+_DIAGNOSTIC = ["text_embedded_newline", "text_nul_and_c_escape", "clean_after_run", "missing_triton", "missing_ssh_keygen",
+               "missing_terraform", "missing_ansible", "missing_terraform_on_clean", "ws_no_terraform_dir", "ws_no_ansible_dir",
+               "ws_no_vars_dir", "ws_clean_without_ansible_dir", "key_name_breaks_the_sed_program", "wait_clock_leading_zero",
+               "count_invalid_via_name", "pkg_arith_operands", "config1_defaults_1worker"]
+EDGE += [dataclasses.replace(sc, name=sc.name + "__bash_setup_sh", invocation="bash setup.sh",
+                             note="started as `bash setup.sh` instead of `./setup.sh`: " + sc.note)
+         for sc in CONFIGS + EDGE if sc.name in _DIAGNOSTIC]
 
 ALL: List[Scenario] = CONFIGS + EDGE
 BY_NAME: Dict[str, Scenario] = {s.name: s for s in ALL}

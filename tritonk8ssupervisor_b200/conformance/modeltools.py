@@ -20,7 +20,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 from .. import bashsem
 from ..runtime import CAPTURE, INHERIT, TO_STDOUT, Runtime
 from ..supervisor import Supervisor
-from .sandbox import Observation, _snapshot, _write
+from .sandbox import Observation, _snapshot, _write, lay_down_home, lay_down_symlinks
 from .scenario import Scenario
 
 _ENV_LOGGED = re.compile(r"^(SDC_|KUBERNETES_|RANCHER_|HOST_PACKAGE=|ANSIBLE_|TRITON_)")
@@ -34,6 +34,11 @@ class ModelRuntime(Runtime):
         self.root = root
         self.env: Dict[str, str] = {"PATH": "/stub/bin:/usr/bin:/bin", "HOME": home, "LC_ALL": "C",
                                     "TK8S_STUB_STATE": "/stub/state", "TK8S_STUB_ROOT": root}
+        sbx = os.path.dirname(home)
+        for key, value in scenario.env.items():
+            self.env[key] = value.replace("<SBX>", sbx)
+        for key in scenario.unset_env:
+            self.env.pop(key, None)
         self._stdin = scenario.stdin.encode("utf-8", "surrogateescape")
         self._pos = 0
         self.stdout: List[str] = []
@@ -64,11 +69,11 @@ class ModelRuntime(Runtime):
         return bashsem.read_builtin(self._next_byte)
 
     # -- clock -------------------------------------------------------------
-    def sleep(self, seconds: int) -> int:
-        return self.run(["sleep", str(seconds)])[0]
+    def sleep(self, seconds: int, where: str = "") -> int:
+        return self.run(["sleep", str(seconds)], where=where)[0]
 
-    def epoch(self) -> str:
-        return self.run(["date", "+%s"], stdout=CAPTURE)[1]
+    def epoch(self, where: str = "") -> Tuple[int, str]:
+        return self.run(["date", "+%s"], stdout=CAPTURE, where=where)
 
     # -- tools -------------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
@@ -91,6 +96,14 @@ class ModelRuntime(Runtime):
             for line in sorted(("%s=%s" % kv for kv in self.env.items()), key=bashsem.c_sort_key):
                 if _ENV_LOGGED.match(line):
                     self.calls.append("  env:" + line)
+        for _ in range(self.sc.stdin_eaters.get("%s-%s" % (tool, args[0] if args else ""), 0)):
+            # a tool that reads the stdin it inherits takes whole lines (stubtool.sh: `read -r`)
+            end = self._stdin.find(b"\n", self._pos)
+            if end == -1:
+                self._pos = len(self._stdin)     # an unterminated tail is consumed, `read` fails, nothing logged
+                break
+            self.calls.append("  stdin:" + bashsem.from_bytes(self._stdin[self._pos:end]))
+            self._pos = end + 1
         status, out, err = self._tool(tool, args, os.path.join(self.root, cwd))
         if stderr == INHERIT:
             self.stderr.append(err)
@@ -208,17 +221,12 @@ class ModelSandbox:
         self.scenario = scenario
         self.tmp = tempfile.mkdtemp(prefix="tk8s-msbx-", dir=base_dir)
         self.workspace = os.path.join(self.tmp, "ws")
-        self.home = os.path.join(self.tmp, "home")
+        self.home = os.path.join(self.tmp, scenario.home_name)
         shutil.copytree(workspace_src, self.workspace, symlinks=True,
                         ignore=shutil.ignore_patterns(".git", "img", "__pycache__"))
         for rel, content in (input_overrides or {}).items():
             _write(os.path.join(self.workspace, rel), content)
-        ssh = os.path.join(self.home, ".ssh")
-        os.makedirs(ssh)
-        for name, content in scenario.ssh_files.items():
-            _write(os.path.join(ssh, name), content)
-        if scenario.known_hosts is not None:
-            _write(os.path.join(ssh, "known_hosts"), scenario.known_hosts)
+        lay_down_home(self.tmp, scenario)
         for rel in scenario.pre_remove:
             p = os.path.join(self.workspace, rel)
             if os.path.isdir(p) and not os.path.islink(p):
@@ -227,17 +235,18 @@ class ModelSandbox:
                 os.remove(p)
         for rel, content in scenario.pre_files.items():
             _write(os.path.join(self.workspace, rel), content)
+        lay_down_symlinks(self.workspace, scenario)
 
     def run(self) -> Observation:
         before = _snapshot(self.workspace)
         rt = ModelRuntime(self.scenario, self.workspace, self.home)
         t0 = time.perf_counter()
-        status = Supervisor(rt, program="setup.sh").main(list(self.scenario.args))
+        status = Supervisor(rt, program=self.scenario.program_label).main(list(self.scenario.args))
         wall = time.perf_counter() - t0
         after = _snapshot(self.workspace)
-        files = {rel: data.decode("utf-8", "surrogateescape") for rel, data in after.items() if before.get(rel) != data}
-        removed = sorted(rel for rel in before if rel not in after)
         scrub = lambda s: s.replace(self.tmp, "<SBX>")  # noqa: E731
+        files = {rel: scrub(data.decode("utf-8", "surrogateescape")) for rel, data in after.items() if before.get(rel) != data}
+        removed = sorted(rel for rel in before if rel not in after)
         return Observation(exit_status=status, stdout=scrub("".join(rt.stdout)), stderr=scrub("".join(rt.stderr)),
                            files=files, removed=removed, calls=[scrub(c) for c in rt.calls], wall_s=wall)
 

@@ -23,7 +23,8 @@ PACKAGE_PARENT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath
 
 #: how the replacement is invoked inside the sandbox (cwd = workspace root)
 REPLACEMENT_ARGV = [sys.executable, "-m", "tritonk8ssupervisor_b200"]
-REPLACEMENT_ENV = {"PYTHONPATH": PACKAGE_PARENT, "TK8S_EXTERNAL_CLOCK": "1", "PYTHONDONTWRITEBYTECODE": "1"}
+#: TK8S_PROGRAM is what a launcher passes as "$0" (INTEGRATION.md); <PROGRAM> is filled in per scenario by the sandbox
+REPLACEMENT_ENV = {"PYTHONPATH": PACKAGE_PARENT, "PYTHONDONTWRITEBYTECODE": "1", "TK8S_PROGRAM": "<PROGRAM>"}
 
 
 def load_golden(path: str) -> dict:
@@ -47,7 +48,27 @@ def build_skeleton(doc: dict, dest: str) -> str:
         os.makedirs(os.path.dirname(p), exist_ok=True)
         with open(p, "w", encoding="utf-8") as fh:
             fh.write(doc["inputs"].get(rel, ""))
+    os.makedirs(dest, exist_ok=True)
     return dest
+
+
+def not_reproducible_here(doc: dict) -> str:
+    """Why this fixture cannot be replayed on this machine ('' if it can).  Two
+    scenarios look outside the sandbox by construction: with HOME unset ``~`` is
+    the password-database home of whoever runs the test, with HOME empty it is
+    ``/``; their fixtures were recorded where neither had an ``.ssh`` directory."""
+    import pwd
+    sc = doc["scenario"]
+    if "HOME" in sc.get("unset_env", []):
+        try:
+            home = pwd.getpwuid(os.getuid()).pw_dir
+        except KeyError:
+            home = "/"
+        if "ls: cannot access '%s/.ssh'" % home not in doc["expected"]["stderr"] or os.path.exists(os.path.join(home, ".ssh")):
+            return "recorded for a user whose home has no .ssh; this one's is %s" % home
+    if sc.get("env", {}).get("HOME") == "" and os.path.exists("/.ssh"):
+        return "/.ssh exists on this machine"
+    return ""
 
 
 def replay(doc: dict, argv: Sequence[str] = None, extra_env: Optional[Dict[str, str]] = None

@@ -130,7 +130,31 @@ class Scenario:
     known_hosts: Optional[str] = None
     #: tools that are not installed at all (no stub on PATH): bash says "command not found"
     missing_tools: List[str] = dataclasses.field(default_factory=list)
+    #: how the program is started: "./setup.sh" (README.md:105, the documented way) or
+    #: "bash setup.sh"; bash labels its own diagnostics with the name it was given
+    invocation: str = "./setup.sh"
+    #: extra environment of the run (both implementations), applied over the sandbox's own;
+    #: the token <SBX> in a value stands for the sandbox directory
+    env: Dict[str, str] = dataclasses.field(default_factory=dict)
+    #: variables removed from the environment of the run (e.g. HOME, LC_ALL)
+    unset_env: List[str] = dataclasses.field(default_factory=list)
+    #: name of the home directory inside the sandbox, and directories created next to it
+    #: with the same ~/.ssh content (a HOME of "h*me" beside "home": tilde results are never globbed)
+    home_name: str = "home"
+    home_decoys: List[str] = dataclasses.field(default_factory=list)
+    #: symbolic links present in the workspace before the run (relative path -> target)
+    pre_symlinks: Dict[str, str] = dataclasses.field(default_factory=dict)
+    #: tools that read the stdin they inherit: "<tool>-<first arg>" -> number of lines taken
+    stdin_eaters: Dict[str, int] = dataclasses.field(default_factory=dict)
     note: str = ""
+
+    @property
+    def program_label(self) -> str:
+        """What bash puts in front of "line N:" for this invocation."""
+        return "setup.sh" if self.invocation == "bash setup.sh" else self.invocation
+
+    def reference_argv(self) -> List[str]:
+        return self.invocation.split(" ")
 
     def to_json(self) -> dict:
         return dataclasses.asdict(self)

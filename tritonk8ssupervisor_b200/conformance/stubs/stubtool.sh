@@ -38,8 +38,20 @@ if [ -f "$S/latency_ms/$tool" ]; then
     /bin/sleep "$(printf '%d.%03d' $((ms / 1000)) $((ms % 1000)))"
 fi
 
-# scripted failure: a file fail/<tool>-<first arg> holding the exit status
 sub=${1:-}
+# a tool that reads the stdin it inherits (terraform asking for approval, ssh
+# without -n): a file eat/<tool>-<first arg> holding the number of lines it takes.
+# The script's remaining answers are what such a tool consumes.
+if [ -f "$S/eat/$tool-$sub" ]; then
+    want=$(cat "$S/eat/$tool-$sub")
+    got=0
+    while [ "$got" -lt "$want" ] && IFS= read -r eaten; do
+        printf '  stdin:%s\n' "$eaten" >> "$S/calls.log"
+        got=$((got + 1))
+    done
+fi
+
+# scripted failure: a file fail/<tool>-<first arg> holding the exit status
 if [ -f "$S/fail/$tool-$sub" ]; then
     msg="$S/fail/$tool-$sub.stderr"
     [ -f "$msg" ] && cat "$msg" >&2

@@ -136,10 +136,14 @@ class Modules:
     """Simulated module implementations.  ``address_map`` maps the authority a
     role uses (``"10.0.0.1:8080"``) to where the mock really listens."""
 
-    def __init__(self, playbook_dir: str, address_map: Dict[str, str], rancher_up_after: int = 2):
+    def __init__(self, playbook_dir: str, address_map: Dict[str, str], rancher_up_after: int = 2,
+                 agent_bootstrap_fails: bool = False):
         self.dir = playbook_dir
         self.address_map = address_map
         self.rancher_up_after = rancher_up_after
+        #: the bootstrap container exits without starting the long-lived agent
+        #: (bad token, server not ready): `docker ps -a` then shows it alone
+        self.agent_bootstrap_fails = agent_bootstrap_fails
         self.paused_s = 0
 
     def run(self, module: str, args: Dict[str, Any], host: SimHost, local: bool) -> Dict[str, Any]:
@@ -205,13 +209,23 @@ class Modules:
 
     # -- containers ----------------------------------------------------------
     def m_docker_container(self, args, host, local):
+        """``state: started``: nothing to do for a running container with the same
+        settings; one that has exited is started again; one whose settings differ
+        (a new registration URL as ``command``) is recreated."""
         name = str(args["name"])
-        if any(c["name"] == name for c in host.containers):
-            return {"changed": False}
-        host.containers.append({"name": name, "image": args.get("image"), "command": args.get("command"),
-                                "privileged": args.get("privileged"), "volumes": args.get("volumes"),
-                                "published_ports": args.get("published_ports"), "restart_policy": args.get("restart_policy")})
-        if str(args.get("image", "")).startswith("rancher/agent"):
+        wanted = {"name": name, "image": args.get("image"), "command": args.get("command"),
+                  "privileged": args.get("privileged"), "volumes": args.get("volumes"),
+                  "published_ports": args.get("published_ports"), "restart_policy": args.get("restart_policy")}
+        one_shot = str(args.get("image", "")).startswith("rancher/agent")     # registers the host, then exits
+        for c in host.containers:
+            if c["name"] == name:
+                same = all(c.get(k) == v for k, v in wanted.items())
+                if same and c.get("running", True):
+                    return {"changed": False}
+                host.containers.remove(c)
+                break
+        host.containers.append(dict(wanted, running=not one_shot))
+        if one_shot and not self.agent_bootstrap_fails and not any(c["name"] == "rancher-agent" for c in host.containers):
             # the bootstrap container starts the long-lived agent
             host.containers.append({"name": "rancher-agent", "image": args.get("image"), "command": "run"})
         return {"changed": True}
@@ -219,7 +233,7 @@ class Modules:
     def m_docker(self, args, host, local):
         """The pre-2.1 ``docker`` module (rancherhost/tasks/main.yml:27): unnamed container."""
         args = dict(args)
-        args.setdefault("name", "rancher-agent-bootstrap" if str(args.get("image", "")).startswith("rancher/agent") else "unnamed")
+        args.setdefault("name", "pensive_curie%d" % len(host.containers))     # docker invents a name
         return self.m_docker_container(args, host, local)
 
     # -- misc ------------------------------------------------------------------
@@ -306,14 +320,14 @@ class DryRun:
 
     def __init__(self, playbook: str, inventory: Inventory, address_map: Dict[str, str],
                  hosts: Optional[Dict[str, SimHost]] = None, rancher_up_after: int = 2,
-                 unreachable: Optional[Dict[str, str]] = None):
+                 unreachable: Optional[Dict[str, str]] = None, agent_bootstrap_fails: bool = False):
         self.playbook = os.path.abspath(playbook)
         self.dir = os.path.dirname(self.playbook)
         self.inventory = inventory
         self.hosts: Dict[str, SimHost] = hosts if hosts is not None else {}
         for h in inventory.host_order:
             self.hosts.setdefault(h, SimHost(h))
-        self.modules = Modules(self.dir, address_map, rancher_up_after)
+        self.modules = Modules(self.dir, address_map, rancher_up_after, agent_bootstrap_fails)
         self.templar = Templar()
         self.events: List[Tuple[str, str, str, str]] = []
         self.hostvars: Dict[str, Dict[str, Any]] = {h: {} for h in self.hosts}

@@ -17,6 +17,8 @@ under bash.
 from __future__ import annotations
 
 import os
+import pwd
+import signal
 import subprocess
 import time
 from typing import Dict, Optional, Sequence, Tuple
@@ -59,11 +61,12 @@ class Runtime:
         the tool is not installed."""
         raise NotImplementedError
 
-    def sleep(self, seconds: int) -> int:
+    def sleep(self, seconds: int, where: str = "") -> int:
+        """``sleep N``; returns its exit status."""
         raise NotImplementedError
 
-    def epoch(self) -> str:
-        """Output of ``date +%s`` (with its newline)."""
+    def epoch(self, where: str = "") -> Tuple[int, str]:
+        """Exit status and output (with its newline) of ``date +%s``."""
         raise NotImplementedError
 
     # -- filesystem (all paths relative to the workspace root) --------------
@@ -85,28 +88,35 @@ class Runtime:
         with open(self.path(rel), "ab") as fh:
             fh.write(bashsem.to_bytes(text))
 
-    def home(self) -> str:
-        return self.env.get("HOME", "")
+    def passwd_home(self) -> str:
+        """The user's home directory according to the password database: what
+        bash expands ``~`` to when ``HOME`` is unset (setup.sh:216-217)."""
+        try:
+            return pwd.getpwuid(os.getuid()).pw_dir
+        except KeyError:
+            return "/"
 
 
 class HostRuntime(Runtime):
     """The real thing: fds 0/1/2, ``subprocess``, wall clock.
 
-    ``external_clock`` makes ``sleep`` and ``date +%s`` child processes found on
-    ``PATH`` (what the reference does, setup.sh:36,62,64) instead of in-process
-    calls, so a scripted ``date``/``sleep`` on ``PATH`` controls time in offline
-    runs.  It is switched on with ``TK8S_EXTERNAL_CLOCK=1``.
+    ``sleep`` and ``date +%s`` are child processes found on ``PATH``, exactly as
+    in the reference (setup.sh:36,41,46,63,64): same child-process trace, and a
+    scripted ``date``/``sleep`` on ``PATH`` controls time in offline runs.
+    ``inprocess_clock`` (``TK8S_INPROCESS_CLOCK=1``) replaces both by in-process
+    calls: ~2 fork/execs fewer per second of waiting, at the price of a trace
+    that differs from the reference's; like the table cache it is opt-in.
     """
 
     def __init__(self, root: str = ".", env: Optional[Dict[str, str]] = None,
                  stdin_fd: int = 0, stdout_fd: int = 1, stderr_fd: int = 2,
-                 external_clock: Optional[bool] = None):
+                 inprocess_clock: Optional[bool] = None):
         self.root = root
         self.env = dict(os.environ if env is None else env)
         self.stdin_fd, self.stdout_fd, self.stderr_fd = stdin_fd, stdout_fd, stderr_fd
-        if external_clock is None:
-            external_clock = self.env.get("TK8S_EXTERNAL_CLOCK", "") == "1"
-        self.external_clock = external_clock
+        if inprocess_clock is None:
+            inprocess_clock = self.env.get("TK8S_INPROCESS_CLOCK", "") == "1"
+        self.inprocess_clock = inprocess_clock
         try:
             self._tty = os.isatty(stdin_fd)
         except OSError:
@@ -150,22 +160,38 @@ class HostRuntime(Runtime):
             elif stderr == TO_STDOUT:
                 self.out(msg)
             return (127 if missing else 126), ""
-        data, _ = proc.communicate()
+        data = None
+        try:
+            data, _ = proc.communicate()
+        except KeyboardInterrupt:
+            # Ctrl-C goes to the whole foreground process group, the child included.
+            # bash waits for the child to finish whatever it does about it (terraform
+            # saving its state) before acting itself; so do we.
+            while True:
+                try:
+                    proc.wait()
+                    break
+                except KeyboardInterrupt:
+                    continue
+            if proc.returncode == -signal.SIGINT:
+                raise                       # the child died of it: so does the script
+            if proc.stdout is not None:
+                data = proc.stdout.read()
         status = proc.returncode
         if status < 0:
             status = 128 - status
         return status, (bashsem.from_bytes(data) if data is not None else "")
 
-    def sleep(self, seconds: int) -> int:
-        if self.external_clock:
-            return self.run(["sleep", str(seconds)])[0]
-        time.sleep(seconds)
-        return 0
+    def sleep(self, seconds: int, where: str = "") -> int:
+        if self.inprocess_clock:
+            time.sleep(seconds)
+            return 0
+        return self.run(["sleep", str(seconds)], where=where)[0]
 
-    def epoch(self) -> str:
-        if self.external_clock:
-            return self.run(["date", "+%s"], stdout=CAPTURE)[1]
-        return "%d\n" % int(time.time())
+    def epoch(self, where: str = "") -> Tuple[int, str]:
+        if self.inprocess_clock:
+            return 0, "%d\n" % int(time.time())
+        return self.run(["date", "+%s"], stdout=CAPTURE, where=where)
 
 
 def _write_all(fd: int, data: bytes) -> None:

@@ -43,6 +43,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 from . import bashsem as sh
 from . import sedprog
 from . import textops as tx
+from .basharith import ArithAbort, ArithError, ArithFatal, ArithRefused, Evaluator
 from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
 from .tritonenv import TritonEnvError, apply_triton_env
 
@@ -54,17 +55,11 @@ INDEX_LIST_RE = r"^[1-9][0-9]?(,[1-9][0-9]?)*$"              # setup.sh:337,380 
 INDEX_RE = r"^[1-9][0-9]*$"                                  # setup.sh:428
 _IDENT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
 
+#: environment variables that configure this program and nothing else
+OWN_ENV = ("TK8S_PROGRAM", "TK8S_CACHE_TRITON", "TK8S_INPROCESS_CLOCK")
+
 TRITON_NETWORKS = ["triton", "networks", "-oname,id"]
 TRITON_PACKAGES = ["triton", "packages", "-oname,id"]
-
-
-def _to_int64(text: str) -> int:
-    """bash arithmetic on a decimal literal: wraps modulo 2**64 (signed).
-    Anything else evaluates like an unset variable name, i.e. 0."""
-    if not re.fullmatch(r"[0-9]+", text):
-        return 0
-    v = int(text) & 0xFFFFFFFFFFFFFFFF
-    return v - (1 << 64) if v >= (1 << 63) else v
 
 
 class _ShellVars(dict):
@@ -84,13 +79,21 @@ class _ShellVars(dict):
 class Supervisor:
     """One run of the path against a :class:`Runtime`."""
 
-    def __init__(self, rt: Runtime, program: str = "setup.sh"):
+    def __init__(self, rt: Runtime, program: str = "./setup.sh"):
         self.rt = rt
+        #: how the script was invoked: bash labels its diagnostics with it
+        #: ("./setup.sh: line 546: export: ...", README.md:105)
         self.program = program
+        self.cache_triton = rt.env.get("TK8S_CACHE_TRITON", "") == "1"
+        # the replacement's own switches are not part of the environment the
+        # reference's children see
+        for knob in OWN_ENV:
+            rt.env.pop(knob, None)
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
-        self.cache_triton = rt.env.get("TK8S_CACHE_TRITON", "") == "1"
         self._tables: Dict[tuple, str] = {}
+        self._lineno = 0
+        self._evaluator = Evaluator(self._arith_get, self.v.__setitem__, errexit=True)   # setup.sh:3
 
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
@@ -141,9 +144,69 @@ class Supervisor:
         if status != 0:
             raise ScriptExit(status)
 
+    def home(self) -> str:
+        """What ``~`` stands for: ``$HOME``, set-but-empty included; the password
+        database entry when HOME is unset."""
+        return self.v["HOME"] if "HOME" in self.v else self.rt.passwd_home()
+
     def tilde(self, path: str) -> str:
         """Tilde expansion of a word starting with ``~/``."""
-        return self.rt.home() + path[1:] if path.startswith("~/") or path == "~" else path
+        return self.home() + path[1:] if path.startswith("~/") or path == "~" else path
+
+    # -- arithmetic on data (basharith) ----------------------------------------
+    def _arith_get(self, name: str) -> Optional[str]:
+        if name == "LINENO":
+            return str(self._lineno)
+        if name in self.v:
+            return self.v[name]
+        return self._bash_variable(name)
+
+    def _bash_variable(self, name: str) -> Optional[str]:
+        """The few variables bash provides by itself that have a fixed value at
+        the places where the path evaluates data (INTEGRATION.md lists what is
+        not modelled: RANDOM, SECONDS, BASHPID and the like)."""
+        if name == "HOME":
+            return self.rt.passwd_home()     # set by bash at start-up when unset, not exported
+        if name in ("OPTIND", "OPTERR"):
+            return "1"
+        if name == "IFS":
+            return " \t\n"
+        if name in ("UID", "EUID"):
+            return str(os.getuid() if name == "UID" else os.geteuid())
+        if name == "PPID":
+            return str(os.getppid())
+        if name == "BASH_SUBSHELL":
+            return "0"
+        if name == "FUNCNAME":
+            return "main"
+        if name == "PWD":
+            return os.path.abspath(self.rt.root)
+        return None
+
+    def arith_eval(self, expr: str, lineno: int, command: str, last_status: int = 0) -> Optional[int]:
+        """Value of an arithmetic expression evaluated by ``command`` (``((`` or
+        ``[[``) at reference line ``lineno``; None after bash's diagnostic when
+        the expression is in error (the command then fails, it does not end the
+        script by itself).  ``last_status`` is the status of the command that ran
+        just before, which is what the script exits with if the evaluation trips
+        over something that is fatal under ``set -e``."""
+        self._lineno = lineno
+        try:
+            return self._evaluator.evaluate(expr)
+        except ArithError as exc:
+            self.rt.err("%s: %s: %s\n" % (self.at(lineno), command, exc.text))
+            return None
+        except ArithAbort as exc:
+            # an error inside an array subscript: bash drops the whole top-level
+            # command, which for this script is `main "$@"`
+            self.rt.err("%s: %s\n" % (self.at(lineno), exc.text))
+            raise ScriptExit(1)
+        except ArithFatal as exc:
+            self.rt.err("%s: %s\n" % (self.at(lineno), exc.text))
+            raise ScriptExit(last_status or 1)
+        except ArithRefused as exc:
+            self.rt.err("%s: %s\n" % (self.program, exc))
+            raise ScriptExit(2)
 
     # ------------------------------------------------------------------
     # main  (setup.sh:8-92)
@@ -172,11 +235,11 @@ class Supervisor:
         self.set_config_to_file()
         self.export_vars()
 
-        self.banner("Starting terraform tasks...")
+        self.banner("Starting terraform tasks...", 36)
         self.run_terraform_tasks()
-        self.banner("Creating ansible configs...")
+        self.banner("Creating ansible configs...", 41)
         self.create_ansible_configs()
-        self.banner("Running ansible tasks...")
+        self.banner("Running ansible tasks...", 46)
         self.run_ansible()
 
         master = self.cat_subst("terraform/masters.ip")
@@ -200,11 +263,11 @@ class Supervisor:
         self.echo("")
         self.echo("    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!")
 
-    def banner(self, text: str) -> None:
+    def banner(self, text: str, line: int = 0) -> None:
         self.echo(RULE)
         self.echo("### " + text)
         self.echo(RULE)
-        self.must(self.rt.sleep(2))
+        self.must(self.rt.sleep(2, self.at(line)))
 
     # ------------------------------------------------------------------
     # a1  setVarDefaults  (setup.sh:240-254)
@@ -231,7 +294,7 @@ class Supervisor:
         rt, v = self.rt, self.v
         _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210))  # status is swallowed by eval "$(...)"
         try:
-            apply_triton_env(sh.cmdsubst(text), v, rt.env)
+            apply_triton_env(sh.cmdsubst(text), v, rt.env, home=rt.passwd_home)
         except TritonEnvError as exc:
             rt.err("%s: %s\n" % (self.program, exc))
             raise ScriptExit(2)
@@ -243,7 +306,9 @@ class Supervisor:
         for f in self.args_of(self._ls_ssh_dir()):
             # ~/.ssh/$(echo $f | sed 's/.pub$//') -- unquoted, so it can be several words
             stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, rt.root), r".pub$", ""))
-            key_args = sh.expand_word([(self.tilde("~/.ssh/"), False), (stem, True)], rt.root)
+            v["f"] = f                                 # the loop variable is a global of the script
+            # tilde expansion yields quoted text: never split, never globbed
+            key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], rt.root)
             _, out = rt.run(["ssh-keygen", "-E", "md5", "-lf"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
             fp = sh.cmdsubst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""))
             if fp == key_id:
@@ -315,10 +380,11 @@ class Supervisor:
         self._tables[key] = text
         return text
 
-    def _print_menu(self, rows: str, default_prefix: Optional[str]) -> Tuple[int, int]:
+    def _print_menu(self, rows: str, default_prefix: Optional[str], loop_var: str) -> Tuple[int, int]:
         """Numbered menu; returns (row count, 1-based position of the default row)."""
         count, default_at = 0, 1
         for row in self.args_of(rows):
+            self.v[loop_var] = row
             count += 1
             shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.rt.root), r"=", "  ", count=0))
             self.rt.out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]))
@@ -376,7 +442,7 @@ class Supervisor:
             lineno = 332 if first else 375
             self.echo(DASHES)
             self.echo("From the networks below:")
-            count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None)
+            count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None, "network")
             if first:
                 public_at = at
             if v[var] == "":
@@ -385,7 +451,7 @@ class Supervisor:
 
         self.echo(DASHES)
         self.echo("From the packages below:")
-        count, package_at = self._print_menu(packages, "k4-highcpu-kvm-7.75G=")
+        count, package_at = self._print_menu(packages, "k4-highcpu-kvm-7.75G=", "package")
         if v["HOST_PACKAGE"] == "":
             v["HOST_PACKAGE"] = self.package_id(self.args_of(str(package_at)))
         self._prompt_package(count)
@@ -397,12 +463,21 @@ class Supervisor:
         t = tx.uniq(tx.sort_lines(tx.tr(sh.echo_unquoted(value, self.rt.root), ",", "\n")))
         return sh.cmdsubst(tx.sed_sub(tx.tr(t, "\n", ","), r"^(.*),$", r"\1"))
 
-    def _out_of_range(self, items: List[str], count: int) -> int:
-        """How many of ``items`` fall outside 1..count (bash 64-bit arithmetic)."""
+    def _out_of_range(self, items: List[str], count: int, var: str, lineno: int) -> int:
+        """How many of ``items`` fall outside 1..count by
+        ``[[ "$item" -gt "$count" || "$item" -lt 1 ]]`` (setup.sh:340,383,431).
+        ``-gt``/``-lt`` inside ``[[ ]]`` evaluate their operands as arithmetic
+        expressions; one bash cannot evaluate makes that test false after a
+        message, so such an item counts as in range -- twice, once per test."""
         bad = 0
         for item in items:
-            n = _to_int64(item)
-            if n > count or n < 1:
+            self.v[var] = item                      # the loop variable is a global of the script
+            n = self.arith_eval(item, lineno, "[[")
+            if n is not None and n > count:
+                bad += 1
+                continue
+            n = self.arith_eval(item, lineno, "[[")
+            if n is not None and n < 1:
                 bad += 1
         return bad
 
@@ -413,11 +488,11 @@ class Supervisor:
         while True:
             answer = self.get_argument(message, self.unq(v[var]), lineno)
             v[var] = self._normalise_list(v[var])
-            answer = self._normalise_list(answer)
+            answer = v["tmp_" + var] = self._normalise_list(answer)
             shown = sh.echo_unquoted(answer, self.rt.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_LIST_RE)) != "":
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
-                bad = self._out_of_range(items, count)
+                bad = self._out_of_range(items, count, "network", lineno + 8)
                 for _ in range(bad):
                     for line in errors:
                         self.echo(line)
@@ -435,11 +510,12 @@ class Supervisor:
         errors = ["error: Enter a valid option or leave blank to use the default.",
                   "    Value should be between 1 and %d." % count]
         while True:
-            answer = self.get_argument("What KVM package should the master and nodes run on:", self.unq(v["HOST_PACKAGE"]), 425)
+            answer = v["tmp_HOST_PACKAGE"] = self.get_argument("What KVM package should the master and nodes run on:",
+                                                               self.unq(v["HOST_PACKAGE"]), 425)
             shown = sh.echo_unquoted(answer, self.rt.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_RE)) != "":
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
-                bad = self._out_of_range(items, count)
+                bad = self._out_of_range(items, count, "package", 431)
                 for _ in range(bad):
                     for line in errors:
                         self.echo(line)
@@ -480,6 +556,9 @@ class Supervisor:
 
     def _nth_row(self, rows: str, index: str) -> str:
         """``sed -n "${index}p"``."""
+        if index.startswith("-e"):
+            # the word is then an option: -e with the script "<rest>p"
+            index = index[2:]
         if not re.fullmatch(r"[0-9]+", index):
             if index == "":
                 # `sed -n p` prints every row
@@ -511,6 +590,7 @@ class Supervisor:
         self.echo("WARN: Make sure that the nodes and master are part of networks that can communicate with each other and this system from which the setup is running.")
         while True:
             yn, ok = self.rt.read("Is the above config correct (yes | no)? ")
+            v["yn"] = yn
             if not ok:
                 raise ScriptExit(1)  # read fails at EOF and errexit ends the run
             if yn == "yes":
@@ -551,6 +631,7 @@ class Supervisor:
 
         while True:
             line, ok = sh.read_builtin(next_byte)
+            self.v["line"] = line
             if not ok:
                 break
             self._export(line)
@@ -583,25 +664,23 @@ class Supervisor:
         self.update_terraform_config(["provider", "triton"])
         self.echo("    Master hostname: %s" % v.get("RANCHER_MASTER_HOSTNAME", ""))  # quotes and all (setup.sh:146)
         self.update_terraform_config(["master"] + self.args_of(self.unq(v.get("RANCHER_MASTER_HOSTNAME", ""))))
-        prefix = v.get("KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "")
-        i = 1
-        while i <= self._arith(v.get("KUBERNETES_NUMBER_OF_NODES", "")):
-            self.echo("    Kubernetes node %d: %s%d" % (i, self.unq(prefix), i))
-            self.update_terraform_config(["host"] + self.args_of(self.unq("%s%d" % (prefix, i))))
-            i += 1
+        # for (( i = 1; i <= $KUBERNETES_NUMBER_OF_NODES; i++ )): the count is text
+        # from ./config spliced into the test expression, `i` a global of the script
+        self.arith_eval("i = 1", 148, "((")
+        while True:
+            more = self.arith_eval("i <= %s" % v.get("KUBERNETES_NUMBER_OF_NODES", ""), 148, "((")
+            if more is None or more == 0:
+                break                 # an arithmetic error fails the `for` command, which errexit lets pass
+
+            i = v.get("i", "")
+            prefix = v.get("KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "")
+            self.echo("    Kubernetes node %s: %s%s" % (i, self.unq(prefix), i))
+            self.update_terraform_config(["host"] + self.args_of(self.unq("%s%s" % (prefix, i))))
+            self.arith_eval("i++", 148, "((")
         self.echo("Starting terraform tasks")
         self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156))[0])
         self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157))[0])
         self.echo("    terraform tasks completed")
-
-    def _arith(self, text: str) -> int:
-        t = text.strip()
-        if re.fullmatch(r"[0-9]+", t):
-            return _to_int64(t)
-        if t == "":
-            return 0
-        self.rt.err("%s: ((: i <= %s: syntax error in expression\n" % (self.program, text))
-        raise ScriptExit(1)
 
     def update_terraform_config(self, args: List[str]) -> None:
         """One block of ``terraform/rancher.tf``.  ``provider`` truncates the
@@ -667,7 +746,7 @@ class Supervisor:
         self.echo("    created: ansible/hosts")
 
         vars_yml = "ansible/roles/ranchermaster/vars/vars.yml"
-        master = sh.cmdsubst(tx.tail_1(rt.read_text("terraform/masters.ip")))
+        master = v["master"] = sh.cmdsubst(tx.tail_1(rt.read_text("terraform/masters.ip")))
         try:
             rt.write_text(vars_yml, sh.echo_builtin(["master: %s" % master]))
         except OSError as exc:
@@ -741,32 +820,43 @@ class Supervisor:
         when the nodes run exactly two dashboard containers and the proxy
         answers "Service Unavailable", stop the stuck pod container on every
         node that has one (upstream-bug workaround, setup.sh:69-82)."""
-        rt = self.rt
+        rt, v = self.rt, self.v
+        v["KUBERNETES_DASHBOARD_UP"], v["DASHBOARD_CONTAINER_COUNT"] = "false", "0"
         up = False
         while not up:
             rt.out(".")
-            self.must(rt.sleep(1))
-            now = sh.cmdsubst(rt.epoch())
-            if not re.fullmatch(r"[0-9]+", now) or int(now) % 15 != 0:
+            self.must(rt.sleep(1, self.at(63)))
+            # if ! ((`date +%s` % 15)): the clock reading is spliced into an arithmetic
+            # expression.  Zero -- or an expression bash cannot evaluate -- means "poll now".
+            date_status, now = rt.epoch(self.at(64))
+            v["_"] = "1"                               # last argument of `sleep 1`
+            remainder = self.arith_eval("%s %% 15" % sh.cmdsubst(now), 64, "((", date_status)
+            if remainder is not None and remainder != 0:
                 continue
+            v["DASHBOARD_CONTAINER_COUNT"] = "0"
             status, body = self._curl_dashboard(66)
             self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
-            shown = sh.echo_unquoted(sh.cmdsubst(body), rt.root)
+            v["cRetVal"] = sh.cmdsubst(body)
+            shown = sh.echo_unquoted(v["cRetVal"], rt.root)
             if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True)) != 0:
                 up = True
+                v["KUBERNETES_DASHBOARD_UP"] = "true"
                 continue
             count = 0
             for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
-                ps = tx.grep(self._ssh_docker_ps(node, 70), r"kubernetes-dashboard")
+                v["node"] = node
+                ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard")
                 count += tx.wc_w(tx.awk_print_field(ps, 1))
+                v["DASHBOARD_CONTAINER_COUNT"] = str(count)
             if count != 2:
                 continue
-            _, body = self._curl_dashboard(72)
+            _, body = self._curl_dashboard(74)
             if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True)) == 0:
                 continue
             for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
-                ps = tx.grep(self._ssh_docker_ps(node, 74), r"k8s_POD.*dashboard")
-                container = sh.cmdsubst(tx.awk_print_field(ps, 1))
+                v["node"] = node
+                ps = tx.grep(self._ssh_docker_ps(node, 76), r"k8s_POD.*dashboard")
+                container = v["dashboard_container"] = sh.cmdsubst(tx.awk_print_field(ps, 1))
                 if container != "":
                     status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,
                                         "docker stop -t0 %s" % container], stdout=DEVNULL, stderr=DEVNULL)
@@ -793,6 +883,7 @@ class Supervisor:
                 yn, ok = rt.read("Do you wish to destroy the KVMs and reset configuration (yes | no)? ")
             else:
                 yn, ok = rt.read("Do you wish to reset configuration (yes | no)? ")
+            self.v["yn"] = yn
             if not ok:
                 raise ScriptExit(1)
             if yn == "yes":
@@ -812,6 +903,7 @@ class Supervisor:
                 and os.path.exists(self.tilde("~/.ssh/known_hosts"))):
             recorded = sh.cmdsubst(rt.read_text("terraform/hosts.ip") + rt.read_text("terraform/masters.ip"))
             for host_key in self.args_of(recorded):
+                self.v["host_key"] = host_key
                 # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped
                 status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT, where=self.at(506))
                 self.must(status)

@@ -2,36 +2,72 @@
 
 The reference does ``eval "$(triton env)"`` (setup.sh:210), i.e. it executes
 whatever the CLI prints.  What the CLI prints is a fixed, tiny dialect --
-``export NAME="value"``, ``unset NAME`` and ``#`` comments -- and that dialect
-is what is accepted here; anything else is refused loudly instead of executed.
-That is the one deliberate narrowing of the boundary ("Deviations").
+``export NAME="value"``, ``unset NAME`` and ``#`` comments -- and that dialect,
+widened by everything that executes nothing (quoting, ``NAME=value``, ``$NAME``
+and ``${NAME}`` references, ``~`` in assignments), is what is accepted here.
+What would run something -- command substitution, backquotes, arithmetic,
+pipes, redirections, commands -- is refused loudly instead of executed.  That is
+the one deliberate narrowing of the boundary ("Deviations").
 """
 from __future__ import annotations
 
+import pwd
 import re
-from typing import Dict, List
+from typing import Callable, Dict, List, Optional, Tuple, Union
 
 _NAME = re.compile(r"[A-Za-z_][A-Za-z0-9_]*\Z")
+_NAME_AT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
 
 
 class TritonEnvError(ValueError):
     pass
 
 
-def _split_commands(text: str) -> List[List[str]]:
+class _Var:
+    """``$NAME`` / ``${NAME}`` waiting for its value; ``quoted``: inside double quotes."""
+
+    def __init__(self, name: str, quoted: bool):
+        self.name, self.quoted = name, quoted
+
+
+#: a word is a sequence of (character, quoted?) pairs and parameter references
+_Piece = Union[Tuple[str, bool], _Var]
+
+
+def _parameter(text: str, i: int, quoted: bool) -> Tuple[Optional[_Var], int]:
+    """The expansion starting at the ``$`` at ``text[i]``.  Plain parameter
+    references are the only expansions that execute nothing, so they are the
+    only ones accepted; a ``$`` that starts no expansion is itself."""
+    nxt = text[i + 1] if i + 1 < len(text) else ""
+    if nxt == "{":
+        m = _NAME_AT.match(text, i + 2)
+        if m and m.end() < len(text) and text[m.end()] == "}":
+            return _Var(m.group(0), quoted), m.end() + 1
+        raise TritonEnvError("refusing to evaluate an expansion in `triton env` output: %r" % text[i:i + 20])
+    m = _NAME_AT.match(text, i + 1)
+    if m and m.group(0) != "_":
+        return _Var(m.group(0), quoted), m.end()
+    special = nxt != "" and (nxt in "(0123456789?$!#@*-_" or (nxt in "'\"" and not quoted))
+    if special:
+        # $(...), positional and special parameters, $'...' and $"..."
+        raise TritonEnvError("refusing to evaluate an expansion in `triton env` output: %r" % text[i:i + 20])
+    return None, i + 1
+
+
+def _split_commands(text: str) -> List[List[List[_Piece]]]:
     """Tokenise into commands (newline or ';' separated), each a list of words,
     honouring single quotes, double quotes and backslashes."""
-    cmds: List[List[str]] = []
-    words: List[str] = []
-    cur: List[str] = []
+    cmds: List[List[List[_Piece]]] = []
+    words: List[List[_Piece]] = []
+    cur: List[_Piece] = []
     have_word = False
     i, n = 0, len(text)
 
     def end_word():
-        nonlocal have_word
+        nonlocal have_word, cur
         if have_word:
-            words.append("".join(cur))
-            cur.clear()
+            words.append(cur)
+            cur = []
             have_word = False
 
     def end_cmd():
@@ -56,7 +92,7 @@ def _split_commands(text: str) -> List[List[str]]:
             j = text.find("'", i + 1)
             if j == -1:
                 raise TritonEnvError("unterminated single quote in `triton env` output")
-            cur.append(text[i + 1:j])
+            cur.extend((ch, True) for ch in text[i + 1:j])
             have_word = True
             i = j + 1
         elif c == '"':
@@ -71,53 +107,144 @@ def _split_commands(text: str) -> List[List[str]]:
                     break
                 if d == "\\" and i + 1 < n and text[i + 1] in '"\\$`\n':
                     if text[i + 1] != "\n":
-                        cur.append(text[i + 1])
+                        cur.append((text[i + 1], True))
                     i += 2
                     continue
-                if d in "$`":
+                if d == "`":
                     raise TritonEnvError("refusing to evaluate an expansion in `triton env` output: %r" % text[i:i + 20])
-                cur.append(d)
+                if d == "$":
+                    var, i = _parameter(text, i, True)
+                    cur.append(var if var is not None else ("$", True))
+                    continue
+                cur.append((d, True))
                 i += 1
         elif c == "\\":
             if i + 1 < n:
                 if text[i + 1] != "\n":
-                    cur.append(text[i + 1])
+                    cur.append((text[i + 1], True))
                     have_word = True
                 i += 2
             else:
                 i += 1
-        elif c in "$`()<>|&":
+        elif c == "$":
+            var, i = _parameter(text, i, False)
+            cur.append(var if var is not None else ("$", False))
+            have_word = True
+        elif c in "`()<>|&":
             raise TritonEnvError("refusing to evaluate shell syntax in `triton env` output: %r" % text[i:i + 20])
         else:
-            cur.append(c)
+            cur.append((c, False))
             have_word = True
             i += 1
     end_cmd()
     return cmds
 
 
-def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str]) -> None:
+def _default_home() -> str:
+    import os
+    try:
+        return pwd.getpwuid(os.getuid()).pw_dir
+    except KeyError:
+        return "/"
+
+
+def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[], str]) -> Optional[Tuple[str, Optional[str]]]:
+    """(name, value) when the word is ``NAME=...`` (value None for a bare ``NAME``);
+    None when it is not an assignment word.  The value is expanded the way bash
+    expands an assignment: parameter references without field splitting or
+    pathname expansion, ``~`` at its start and after each unquoted ``:``."""
+    k = 0
+    while k < len(word) and not isinstance(word[k], _Var) and not word[k][1] and word[k][0] not in "=":
+        k += 1
+    name = "".join(p[0] for p in word[:k])       # type: ignore[index]
+    if not _NAME.match(name):
+        return None
+    if k == len(word):
+        return name, None
+    if isinstance(word[k], _Var) or word[k] != ("=", False):
+        return None
+    out: List[str] = []
+    rest = word[k + 1:]
+    i = 0
+    at_start = True
+    while i < len(rest):
+        p = rest[i]
+        if isinstance(p, _Var):
+            out.append(shell_vars.get(p.name, ""))
+            at_start = False
+            i += 1
+            continue
+        ch, quoted = p
+        if at_start and ch == "~" and not quoted:
+            j = i + 1
+            while j < len(rest) and not isinstance(rest[j], _Var) and not rest[j][1] and rest[j][0] not in "/:":
+                j += 1
+            if j < len(rest) and (isinstance(rest[j], _Var) or rest[j][1]):
+                pass                                  # a quoted character inside the tilde-prefix: no expansion
+            else:
+                user = "".join(q[0] for q in rest[i + 1:j])      # type: ignore[index]
+                if user == "":
+                    out.append(home())
+                    i = j
+                    at_start = False
+                    continue
+                if user in ("+", "-"):
+                    raise TritonEnvError("refusing to evaluate ~%s in `triton env` output" % user)
+                try:
+                    out.append(pwd.getpwnam(user).pw_dir)
+                    i = j
+                    at_start = False
+                    continue
+                except KeyError:
+                    pass                              # no such user: the text stays as it is
+        out.append(ch)
+        at_start = ch == ":" and not quoted
+        i += 1
+    return name, "".join(out)
+
+
+def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
+                     home: Optional[Callable[[], str]] = None) -> None:
     """Mutate ``shell_vars`` (all shell variables) and ``env`` (the exported
-    ones) as ``eval`` of ``text`` would for the supported dialect."""
+    ones) as ``eval`` of ``text`` would for the supported dialect.  ``home()``
+    is what ``~`` stands for when ``HOME`` is not among the shell variables."""
+    def tilde_home() -> str:
+        if "HOME" in shell_vars:
+            return shell_vars["HOME"]
+        return (home or _default_home)()
+
+    def plain(word: List[_Piece]) -> str:
+        if any(isinstance(p, _Var) for p in word):
+            # outside an assignment the value would be split into fields and globbed
+            raise TritonEnvError("refusing to expand a parameter outside an assignment in `triton env` output")
+        return "".join(p[0] for p in word)        # type: ignore[index]
+
     for words in _split_commands(text):
-        head = words[0]
+        head = plain(words[0]) if not any(isinstance(p, _Var) for p in words[0]) else None
         if head == "export":
             for w in words[1:]:
-                name, eq, value = w.partition("=")
-                if not _NAME.match(name):
-                    raise TritonEnvError("not a valid identifier in `triton env` output: %r" % w)
-                if eq:
+                parsed = _assignment(w, shell_vars, tilde_home)
+                if parsed is None:
+                    raise TritonEnvError("not a valid identifier in `triton env` output: %r" % _show(w))
+                name, value = parsed
+                if value is not None:
                     shell_vars[name] = value
                 if name in shell_vars:
                     env[name] = shell_vars[name]
         elif head == "unset":
             for w in words[1:]:
-                shell_vars.pop(w, None)
-                env.pop(w, None)
-        elif "=" in head and _NAME.match(head.split("=", 1)[0]) and len(words) == 1:
-            name, _, value = head.partition("=")
+                name = plain(w)
+                shell_vars.pop(name, None)
+                env.pop(name, None)
+        else:
+            parsed = _assignment(words[0], shell_vars, tilde_home) if len(words) == 1 else None
+            if parsed is None or parsed[1] is None:
+                raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(_show(w) for w in words))
+            name, value = parsed
             shell_vars[name] = value
             if name in env:
                 env[name] = value
-        else:
-            raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(words))
+
+
+def _show(word: List[_Piece]) -> str:
+    return "".join("$" + p.name if isinstance(p, _Var) else p[0] for p in word)
