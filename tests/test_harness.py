@@ -35,6 +35,26 @@ def test_count_scaling_extension():
     assert ext["size_law"]["per_worker"] == 234          # +234 bytes per worker block
 
 
+def test_machine_count_must_match_the_run(tmp_path):
+    """Check (ii) holds the plan to 1 master + KUBERNETES_NUMBER_OF_NODES from the run's
+    own ./config, not to a floor: a generator that drops a worker block fails it."""
+    import shutil
+    from tritonk8ssupervisor_b200.conformance.sandbox import Observation
+    doc = harness.golden_for(CONFIGS[1])
+    obs = Observation.from_json(doc["expected"])
+    assert harness.expected_machine_count(obs) == 3
+    ws = tmp_path / "ws"
+    shutil.copytree(harness.WORKSPACE_TEMPLATE, ws)
+    text = obs.files["terraform/rancher.tf"]
+    cut = text[:text.index('\nmodule "kubenode2"')]
+    (ws / "terraform" / "rancher.tf").write_text(cut)
+    (ws / "ansible" / "hosts").write_text(obs.files["ansible/hosts"])
+    (ws / "ansible/roles/ranchermaster/vars/vars.yml").write_text(obs.files["ansible/roles/ranchermaster/vars/vars.yml"])
+    res = harness.ConfigResult(name="dropped")
+    harness.check_generated_tree(str(ws), obs, res)
+    assert not res.terraform and any("2 machines planned, the run asked for 3" in d for d in res.details)
+
+
 def test_a_wrong_implementation_fails_parity(tmp_path):
     """The harness must be able to say no: an implementation that gets one byte
     wrong scores 0 on parity."""
@@ -76,6 +96,15 @@ def test_bench_line_contract():
     assert d["gpu_launches"] == 0 and d["roofline"]["frac"] is None and d["vs_baseline"] is None
     assert "workload" in d["config"]
     assert set(d["e2e"]["median_run_ms_per_config"]) == {c.name for c in CONFIGS}
+    # the whole recorded parity surface rides along, and no criterion is asserted rather than measured
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    n = len(rp.list_goldens())
+    assert d["catalogue"]["replayed"] + d["catalogue"]["skipped_not_reproducible_here"] == n
+    assert d["catalogue"]["passed"] == d["catalogue"]["replayed"] >= n - 2
+    for leg in ("per_config", "per_config_e2e"):
+        assert set(d[leg]) == {c.name for c in CONFIGS}
+        assert all(v["deterministic"] and v["passed"] for v in d[leg].values())
+    assert d["scaling"] == "strong"
 
 
 def test_bench_reference_arm(ref_root):
@@ -105,6 +134,11 @@ def test_bench_two_ranks_gloo():
     d = json.loads(lines[0])
     assert d["n_gpus"] == 2 and d["value"] == 1.0 and d["e2e"]["value"] == 1.0
     assert d["cpu_baseline"]["value"] is None      # baseline is timed at N=1 only
+    # the ranks divide the work instead of repeating it: rank 0 saw 3 of the 5 configs, the sums cover everything
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    assert len(d["per_config"]) == 3
+    assert d["catalogue"]["replayed"] + d["catalogue"]["skipped_not_reproducible_here"] == len(rp.list_goldens())
+    assert d["catalogue"]["passed"] == d["catalogue"]["replayed"]
 
 
 def test_triton_table_cache_changes_only_the_trace():

@@ -83,6 +83,15 @@ def expected_module_names(scenario_obs: Observation) -> List[str]:
     return re.findall(r'^module "([^"]*)" \{$', scenario_obs.files.get("terraform/rancher.tf", ""), re.M)
 
 
+def expected_machine_count(obs: Observation) -> int:
+    """1 master + the node count the run wrote to ./config (setup.sh:202); where the
+    observation carries no ./config (the count-scaling extension), one per IP recorded."""
+    m = re.search(r"^KUBERNETES_NUMBER_OF_NODES=([1-9][0-9]*)$", obs.files.get("config", ""), re.M)
+    if m:
+        return 1 + int(m.group(1))
+    return len((obs.files.get("terraform/masters.ip", "") + obs.files.get("terraform/hosts.ip", "")).split())
+
+
 def check_generated_tree(workspace: str, obs: Observation, res: ConfigResult) -> None:
     """(ii) and (iii) on a workspace that holds the generated files."""
     tf = tfvalidate.validate(os.path.join(workspace, "terraform"))
@@ -96,7 +105,11 @@ def check_generated_tree(workspace: str, obs: Observation, res: ConfigResult) ->
         res.details.append("terraform: plan does not hold one triton_machine per generated module block: %r vs %r"
                            % ([p["address"] for p in planned], names))
     mock_ok = _mock_apply_agrees(workspace, obs, res) if tf.ok else False
-    res.terraform = tf.ok and plan_ok and mock_ok and len(planned) >= 2
+    want_machines = expected_machine_count(obs)
+    if len(planned) != want_machines:
+        res.details.append("terraform: %d machines planned, the run asked for %d (1 master + KUBERNETES_NUMBER_OF_NODES)"
+                           % (len(planned), want_machines))
+    res.terraform = tf.ok and plan_ok and mock_ok and len(planned) == want_machines
 
     hosts_file = os.path.join(workspace, "ansible", "hosts")
     try:
@@ -176,6 +189,30 @@ def golden_for(scenario: Scenario) -> dict:
 def run_all(argv: Optional[Sequence[str]] = None, extra_env: Optional[Dict[str, str]] = None,
             workspace_src: str = WORKSPACE_TEMPLATE, repeat: int = 2) -> List[ConfigResult]:
     return [run_config(golden_for(sc), argv, extra_env, workspace_src, repeat) for sc in CONFIGS]
+
+
+def replay_catalogue(docs: Optional[Sequence[dict]] = None) -> Dict[str, Any]:
+    """The whole recorded parity surface, in-process (about 10 ms a scenario):
+    {"replayed": n, "passed": n, "skipped": [...], "failed": [...]}."""
+    if docs is None:
+        docs = [rp.load_golden(p) for p in rp.list_goldens()]
+    out: Dict[str, Any] = {"replayed": 0, "passed": 0, "skipped": [], "failed": []}
+    for doc in docs:
+        name = doc["scenario"]["name"]
+        if rp.not_reproducible_here(doc):
+            out["skipped"].append(name)
+            continue
+        out["replayed"] += 1
+        try:
+            expected, got = rp.replay_in_process(doc)
+            ok = not expected.diff(got)
+        except Exception:                      # a crash is a failure, not a reason to lose the line
+            ok = False
+        if ok:
+            out["passed"] += 1
+        else:
+            out["failed"].append(name)
+    return out
 
 
 def pass_rate(results: Sequence[ConfigResult]) -> float:
