@@ -377,6 +377,16 @@ EDGE += [
              env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"], note="LANG=C.UTF-8 with LC_ALL unset: same bytes, same order"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
+    Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,
+             env={"SHLVL": "5", "PWD": "/bogus/elsewhere", "OLDPWD": "/nonexistent"},
+             note="what bash exports by itself: SHLVL one up (one down again for the lone command of a $(...)), PWD "
+                  "re-established at start-up and following each cd, an OLDPWD that is no directory dropped"),
+    Scenario(name="env_shell_level_garbage", stdin=BLANK8 + YES, env={"SHLVL": "abc", "OLDPWD": "/tmp"},
+             note="a SHLVL that is no number counts as 0; an OLDPWD that is a directory is passed on until the first cd"),
+    Scenario(name="env_shell_level_too_high", stdin=BLANK8 + YES, env={"SHLVL": "999"},
+             note="shell level 1000: bash warns and resets to 1"),
+    Scenario(name="env_no_locale_at_all", stdin=_answers("caf\u00e9", "", "", "", "", "4,1", "", "", "yes"), unset_env=["LC_ALL"],
+             note="no LC_ALL, no LANG: children must not find an LC_CTYPE that the reference's children do not have"),
     Scenario(name="env_own_switches_do_not_leak", stdin=BLANK8 + YES,
              env={"TK8S_PROGRAM_": "1", "KUBERNETES_TK8S": "kept"},
              note="variables that merely look like the replacement's own switches pass through to terraform/ansible"),

@@ -10,6 +10,7 @@ running the path cannot drift apart.
 """
 from __future__ import annotations
 
+import hashlib
 import os
 import re
 import shutil
@@ -18,12 +19,12 @@ import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 from .. import bashsem
-from ..runtime import CAPTURE, INHERIT, TO_STDOUT, Runtime
+from ..runtime import CAPTURE, INHERIT, TO_STDOUT, Runtime, child_env
 from ..supervisor import Supervisor
 from .sandbox import Observation, _snapshot, _write, lay_down_home, lay_down_symlinks
 from .scenario import Scenario
 
-_ENV_LOGGED = re.compile(r"^(SDC_|KUBERNETES_|RANCHER_|HOST_PACKAGE=|ANSIBLE_|TRITON_)")
+_ENV_HIDDEN = re.compile(r"^(TK8S_STUB_|PYTHON)")
 
 
 class ModelRuntime(Runtime):
@@ -32,9 +33,10 @@ class ModelRuntime(Runtime):
     def __init__(self, scenario: Scenario, root: str, home: str):
         self.sc = scenario
         self.root = root
-        self.env: Dict[str, str] = {"PATH": "/stub/bin:/usr/bin:/bin", "HOME": home, "LC_ALL": "C",
-                                    "TK8S_STUB_STATE": "/stub/state", "TK8S_STUB_ROOT": root}
         sbx = os.path.dirname(home)
+        self.env: Dict[str, str] = {"PATH": sbx + "/bin:/usr/bin:/bin", "HOME": home, "LC_ALL": "C",
+                                    "TK8S_STUB_STATE": sbx + "/state", "TK8S_STUB_ROOT": root}
+        self._sbx = sbx
         for key, value in scenario.env.items():
             self.env[key] = value.replace("<SBX>", sbx)
         for key in scenario.unset_env:
@@ -73,11 +75,11 @@ class ModelRuntime(Runtime):
         return self.run(["sleep", str(seconds)], where=where)[0]
 
     def epoch(self, where: str = "") -> Tuple[int, str]:
-        return self.run(["date", "+%s"], stdout=CAPTURE, where=where)
+        return self.run(["date", "+%s"], stdout=CAPTURE, where=where, lone_subst=True)
 
     # -- tools -------------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
         tool, args = argv[0], list(argv[1:])
         self._n_calls += 1
         if self._n_calls > self.max_calls:
@@ -92,10 +94,16 @@ class ModelRuntime(Runtime):
             return 127, ""
         rel = "." if cwd in (".", "") else "./" + cwd
         self.calls.append("%s|%s|%s" % (tool, rel, " ".join(args)))
+        # what stubtool.sh records of its environment: `env | grep -v | sort | sed`, line by line
+        env = child_env(self.env, "%s/bin/%s" % (self._sbx, tool), lone_subst)
+        dump = "".join("%s=%s\n" % kv for kv in env.items())
+        lines = sorted((l for l in dump.split("\n")[:-1] if not _ENV_HIDDEN.match(l)), key=bashsem.c_sort_key)
+        lines = [l.replace(self._sbx, "<SBX>") for l in lines]
         if tool in ("terraform", "ansible-playbook"):
-            for line in sorted(("%s=%s" % kv for kv in self.env.items()), key=bashsem.c_sort_key):
-                if _ENV_LOGGED.match(line):
-                    self.calls.append("  env:" + line)
+            self.calls.extend("  env:" + l for l in lines)
+        else:
+            digest = hashlib.md5(bashsem.to_bytes("".join(l + "\n" for l in lines))).hexdigest()[:12]
+            self.calls.append("  env~:" + digest)
         for _ in range(self.sc.stdin_eaters.get("%s-%s" % (tool, args[0] if args else ""), 0)):
             # a tool that reads the stdin it inherits takes whole lines (stubtool.sh: `read -r`)
             end = self._stdin.find(b"\n", self._pos)

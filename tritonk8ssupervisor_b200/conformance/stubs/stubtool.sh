@@ -23,12 +23,17 @@ case "$PWD" in
     *) rel=$PWD ;;
 esac
 printf '%s|%s|%s\n' "$tool" "$rel" "$*" >> "$S/calls.log"
-# the provisioning tools also see the exported configuration (setup.sh:543-549):
-# record it, literal double quotes and all
+# What the tool inherits is part of the boundary: every line of ./config exported
+# verbatim, literal double quotes and all (setup.sh:543-549), plus what bash itself
+# exports (SHLVL, PWD and OLDPWD following each `cd`, `_` = path of the command).
+# The provisioning tools get their whole environment recorded, the others a digest
+# of it.  Left out: this stub's own plumbing, and PYTHON* (how the test harness
+# makes an uninstalled Python package importable).
+sbx=${S%/state}
+envdump() { env | grep -v -E '^(TK8S_STUB_|PYTHON)' | LC_ALL=C sort | sed "s|$sbx|<SBX>|g"; }
 case "$tool" in
-    terraform|ansible-playbook)
-        env | grep -E '^(SDC_|KUBERNETES_|RANCHER_|HOST_PACKAGE=|ANSIBLE_|TRITON_)' | LC_ALL=C sort | sed 's/^/  env:/' >> "$S/calls.log"
-        ;;
+    terraform|ansible-playbook) envdump | sed 's/^/  env:/' >> "$S/calls.log" ;;
+    *) printf '  env~:%s\n' "$(envdump | md5sum | cut -c1-12)" >> "$S/calls.log" ;;
 esac
 
 # modelled latency (milliseconds) of a tool that sits on a network round trip:

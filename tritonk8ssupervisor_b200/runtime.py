@@ -55,10 +55,13 @@ class Runtime:
 
     # -- children ----------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
         """Run a tool; returns (exit status, captured stdout or '').  ``where``
         ("setup.sh: line 157") prefixes the shell's own diagnostics, e.g. when
-        the tool is not installed."""
+        the tool is not installed.  ``lone_subst``: the tool is the only command
+        of a ``$(...)`` (``$(triton env)``, ``$(curl ...)``, `` `date +%s` ``):
+        bash then execs it straight from the substitution's subshell, and takes the
+        shell level it had added back out of SHLVL first -- see :func:`child_env`."""
         raise NotImplementedError
 
     def sleep(self, seconds: int, where: str = "") -> int:
@@ -112,7 +115,7 @@ class HostRuntime(Runtime):
                  stdin_fd: int = 0, stdout_fd: int = 1, stderr_fd: int = 2,
                  inprocess_clock: Optional[bool] = None):
         self.root = root
-        self.env = dict(os.environ if env is None else env)
+        self.env = inherited_environment() if env is None else dict(env)
         self.stdin_fd, self.stdout_fd, self.stderr_fd = stdin_fd, stdout_fd, stderr_fd
         if inprocess_clock is None:
             inprocess_clock = self.env.get("TK8S_INPROCESS_CLOCK", "") == "1"
@@ -142,41 +145,50 @@ class HostRuntime(Runtime):
         return bashsem.read_builtin(self._next_byte)
 
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "") -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
         out_target = {INHERIT: self.stdout_fd, DEVNULL: subprocess.DEVNULL,
                       CAPTURE: subprocess.PIPE}[stdout]
         err_target = {INHERIT: self.stderr_fd, DEVNULL: subprocess.DEVNULL,
                       TO_STDOUT: self.stdout_fd}[stderr]
+        # Ctrl-C goes to the whole foreground process group, the child included.  bash
+        # does not act on it while the child runs: it waits for the child to finish
+        # whatever it does about the signal (terraform saving its state), and only
+        # then dies of it itself -- if the child did.  So SIGINT is merely noted from
+        # before the child starts until it has been waited for.  (Letting it raise
+        # KeyboardInterrupt inside Popen.wait() can lose the child's status:
+        # interrupted between waitpid() and the bookkeeping, the retry finds no child
+        # and reports 0.)
+        interrupted: list = []
+        restore = None
         try:
-            proc = subprocess.Popen(list(argv), cwd=self.path(cwd), env=self.env,
-                                    stdin=self.stdin_fd, stdout=out_target, stderr=err_target)
-        except (FileNotFoundError, PermissionError) as exc:
-            # what bash says; the message follows the command's own redirections
-            missing = isinstance(exc, FileNotFoundError)
-            msg = "%s%s: %s\n" % (where + ": " if where else "", argv[0],
-                                  "command not found" if missing else "Permission denied")
-            if stderr == INHERIT:
-                self.err(msg)
-            elif stderr == TO_STDOUT:
-                self.out(msg)
-            return (127 if missing else 126), ""
-        data = None
+            if signal.getsignal(signal.SIGINT) is signal.default_int_handler:
+                signal.signal(signal.SIGINT, lambda signum, frame: interrupted.append(signum))
+                restore = signal.default_int_handler
+        except ValueError:
+            pass                            # not the main thread: signals are not ours to handle
         try:
+            try:
+                exe = find_command(argv[0], self.env.get("PATH"), self.path(cwd))
+                # bash puts the path of the command it starts into the command's environment as `_`
+                proc = subprocess.Popen(list(argv), executable=exe, cwd=self.path(cwd),
+                                        env=child_env(self.env, exe, lone_subst),
+                                        stdin=self.stdin_fd, stdout=out_target, stderr=err_target)
+            except (FileNotFoundError, PermissionError) as exc:
+                # what bash says; the message follows the command's own redirections
+                missing = isinstance(exc, FileNotFoundError)
+                msg = "%s%s: %s\n" % (where + ": " if where else "", argv[0],
+                                      "command not found" if missing else "Permission denied")
+                if stderr == INHERIT:
+                    self.err(msg)
+                elif stderr == TO_STDOUT:
+                    self.out(msg)
+                return (127 if missing else 126), ""
             data, _ = proc.communicate()
-        except KeyboardInterrupt:
-            # Ctrl-C goes to the whole foreground process group, the child included.
-            # bash waits for the child to finish whatever it does about it (terraform
-            # saving its state) before acting itself; so do we.
-            while True:
-                try:
-                    proc.wait()
-                    break
-                except KeyboardInterrupt:
-                    continue
-            if proc.returncode == -signal.SIGINT:
-                raise                       # the child died of it: so does the script
-            if proc.stdout is not None:
-                data = proc.stdout.read()
+        finally:
+            if restore is not None:
+                signal.signal(signal.SIGINT, restore)
+        if interrupted and proc.returncode == -signal.SIGINT:
+            raise KeyboardInterrupt         # the child died of it: so does the script
         status = proc.returncode
         if status < 0:
             status = 128 - status
@@ -191,7 +203,66 @@ class HostRuntime(Runtime):
     def epoch(self, where: str = "") -> Tuple[int, str]:
         if self.inprocess_clock:
             return 0, "%d\n" % int(time.time())
-        return self.run(["date", "+%s"], stdout=CAPTURE, where=where)
+        return self.run(["date", "+%s"], stdout=CAPTURE, where=where, lone_subst=True)
+
+
+def inherited_environment() -> Dict[str, str]:
+    """The environment this process was *started with*.  CPython may add
+    ``LC_CTYPE=C.UTF-8`` to its own environment at start-up (locale coercion,
+    when no locale is configured at all); bash does no such thing, so a variable
+    that was not there when the process was exec'ed is not passed on."""
+    env = dict(os.environ)
+    if "LC_CTYPE" in env:
+        try:
+            with open("/proc/self/environ", "rb") as fh:
+                initial = {item.split(b"=", 1)[0] for item in fh.read().split(b"\0") if b"=" in item}
+            if b"LC_CTYPE" not in initial:
+                del env["LC_CTYPE"]
+        except OSError:
+            pass
+    return env
+
+
+def child_env(env: Dict[str, str], exe: str, lone_subst: bool = False) -> Dict[str, str]:
+    """The environment bash hands a command: the exported variables, ``_`` = the
+    path the command was found at, and -- for the only command of a command
+    substitution -- SHLVL one lower (never below 0)."""
+    out = dict(env, _=exe)
+    if lone_subst:
+        try:
+            out["SHLVL"] = str(max(0, int(env.get("SHLVL", "0")) - 1))
+        except ValueError:
+            out["SHLVL"] = "0"
+    return out
+
+
+#: the search path bash falls back to when PATH is unset
+DEFAULT_PATH = "/usr/local/sbin:/usr/local/bin:/usr/sbin:/usr/bin:/sbin:/bin:."
+
+
+def find_command(name: str, path: Optional[str], cwd: str = ".") -> str:
+    """Where bash finds ``name``: as given when it contains a slash, else the first
+    executable regular file along PATH (an empty element is the current directory).
+    Raises FileNotFoundError, or PermissionError when only non-executable files of
+    that name were met (bash: status 126, "Permission denied")."""
+    if "/" in name:
+        full = name if os.path.isabs(name) else os.path.join(cwd, name)
+        if not os.path.exists(full):
+            raise FileNotFoundError(name)
+        if os.path.isdir(full) or not os.access(full, os.X_OK):
+            raise PermissionError(name)
+        return name
+    denied = False
+    for d in (DEFAULT_PATH if path is None else path).split(":"):
+        cand = os.path.join(d or ".", name)
+        full = cand if os.path.isabs(cand) else os.path.join(cwd, cand)
+        if os.path.isfile(full):
+            if os.access(full, os.X_OK):
+                return cand
+            denied = True
+    if denied:
+        raise PermissionError(name)
+    raise FileNotFoundError(name)
 
 
 def _write_all(fd: int, data: bytes) -> None:

@@ -91,9 +91,49 @@ class Supervisor:
             rt.env.pop(knob, None)
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
+        self._shell_bookkeeping()
         self._tables: Dict[tuple, str] = {}
         self._lineno = 0
         self._evaluator = Evaluator(self._arith_get, self.v.__setitem__, errexit=True)   # setup.sh:3
+
+    # ------------------------------------------------------------------
+    # what bash itself exports to every child: SHLVL, PWD, OLDPWD
+    # (``_``, the path of the command being started, is the runtime's business)
+    # ------------------------------------------------------------------
+    def _shell_bookkeeping(self) -> None:
+        """The script *is* a shell level: children see SHLVL one higher than the
+        caller's, PWD as bash validated it at start-up, and an OLDPWD that does not
+        name a directory is dropped."""
+        env = self.rt.env
+        old = env.get("SHLVL", "")
+        level = (int(old) if re.fullmatch(r"[ \t]*[-+]?[0-9]+[ \t]*", old) else 0) + 1
+        if level < 0:
+            level = 0
+        elif level >= 1000:
+            self.rt.err("bash: warning: shell level (%d) too high, resetting to 1\n" % level)
+            level = 1
+        self.export("SHLVL", str(level))
+        root = os.path.abspath(self.rt.root)
+        pwd = env.get("PWD", "")
+        try:
+            inherited_ok = pwd.startswith("/") and os.path.samefile(pwd, root)
+        except OSError:
+            inherited_ok = False
+        self.export("PWD", pwd if inherited_ok else os.path.realpath(root))
+        if "OLDPWD" in env and not os.path.isdir(env["OLDPWD"]):
+            del env["OLDPWD"]
+            self.v.pop("OLDPWD", None)
+
+    def export(self, name: str, value: str) -> None:
+        self.v[name] = value
+        self.rt.env[name] = value
+
+    def cd(self, rel: str) -> None:
+        """``cd rel``: no process of ours changes directory (children are started
+        with ``cwd=``), but PWD and OLDPWD are part of what they inherit."""
+        old = self.v.get("PWD", "")
+        self.export("OLDPWD", old)
+        self.export("PWD", os.path.normpath(os.path.join(old, rel)))
 
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
@@ -292,7 +332,7 @@ class Supervisor:
     # ------------------------------------------------------------------
     def set_config_from_triton(self) -> None:
         rt, v = self.rt, self.v
-        _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210))  # status is swallowed by eval "$(...)"
+        _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210), lone_subst=True)  # status is swallowed by eval "$(...)"
         try:
             apply_triton_env(sh.cmdsubst(text), v, rt.env, home=rt.passwd_home)
         except TritonEnvError as exc:
@@ -677,10 +717,12 @@ class Supervisor:
             self.echo("    Kubernetes node %s: %s%s" % (i, self.unq(prefix), i))
             self.update_terraform_config(["host"] + self.args_of(self.unq("%s%s" % (prefix, i))))
             self.arith_eval("i++", 148, "((")
+        self.cd("terraform")
         self.echo("Starting terraform tasks")
         self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156))[0])
         self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157))[0])
         self.echo("    terraform tasks completed")
+        self.cd("..")
 
     def update_terraform_config(self, args: List[str]) -> None:
         """One block of ``terraform/rancher.tf``.  ``provider`` truncates the
@@ -754,8 +796,10 @@ class Supervisor:
         self.append_line(vars_yml, 'kubernetes_name: "%s"' % self.unq(v.get("KUBERNETES_NAME", "")))
         self.append_line(vars_yml, 'kubernetes_description: "%s"' % self.unq(v.get("KUBERNETES_DESCRIPTION", "")))
 
+        self.cd("ansible")
         self._rewrite_private_key_file("ansible/ansible.cfg", "ansible/tmp.cfg", ";", self.unq(v.get("SDC_KEY", "")),
                                        shown_src="ansible.cfg")
+        self.cd("..")
         self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml")
 
     def _rewrite_private_key_file(self, cfg: str, tmp: str, delim: str, value: str, shown_src: str,
@@ -793,7 +837,9 @@ class Supervisor:
         if not os.path.isdir(self.rt.path("ansible")):
             self.rt.err("%s: line 112: cd: ansible: No such file or directory\n" % self.program)
             raise ScriptExit(1)
+        self.cd("ansible")
         self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible", where=self.at(113))[0])
+        self.cd("..")
 
     # ------------------------------------------------------------------
     # dashboard wait loop  (setup.sh:59-85)
@@ -807,8 +853,9 @@ class Supervisor:
             ("/kubernetes-dashboard:9090/", False)], self.rt.root)
 
     def _curl_dashboard(self, line: int) -> Tuple[int, str]:
+        # cRetVal=$(curl ...) at :66 holds curl alone; at :74 curl heads a pipeline
         return self.rt.run(["curl", "--connect-timeout", "5", "--max-time", "5", "-s"] + self._dashboard_url_words(),
-                           stdout=CAPTURE, where=self.at(line))
+                           stdout=CAPTURE, where=self.at(line), lone_subst=line == 66)
 
     def _ssh_docker_ps(self, node: str, line: int) -> str:
         return self.rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node, "docker", "ps"],
@@ -897,8 +944,10 @@ class Supervisor:
     def _clean(self) -> None:
         rt = self.rt
         if rt.exists("terraform/rancher.tf"):
+            self.cd("terraform")
             self.echo("    destroying images...")
             rt.run(["terraform", "destroy", "-force"], cwd="terraform", stderr=DEVNULL)  # `|| true`
+            self.cd("..")
         if (rt.exists("terraform/hosts.ip") and rt.exists("terraform/masters.ip")
                 and os.path.exists(self.tilde("~/.ssh/known_hosts"))):
             recorded = sh.cmdsubst(rt.read_text("terraform/hosts.ip") + rt.read_text("terraform/masters.ip"))
