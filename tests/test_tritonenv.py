@@ -74,6 +74,7 @@ def test_same_variables_as_bash_eval(text):
     'export SDC_URL="$((1+1))"\n', 'export SDC_URL="${HOME:-x}"\n', 'export SDC_URL="${HOME"\n', "export SDC_URL=$1\n",
     'export SDC_URL="$?"\n', "export SDC_URL=$'ansi'\n", "unset $HOME\n", "$HOME\n", "export $HOME=x\n", "export SDC_URL=$_\n",
     "export SDC_URL=~+/x\n", "export SDC_URL=${!HOME}\n", "export SDC_URL=$$\n",
+    "export IFS=:\n", "IFS=,\n", "unset IFS\n", "export LC_ALL=en_US.UTF-8\n", "GLOBIGNORE=*\n",
 ])
 def test_everything_else_is_refused(text):
     with pytest.raises(TritonEnvError):

@@ -387,6 +387,14 @@ EDGE += [
              note="shell level 1000: bash warns and resets to 1"),
     Scenario(name="env_no_locale_at_all", stdin=_answers("caf\u00e9", "", "", "", "", "4,1", "", "", "yes"), unset_env=["LC_ALL"],
              note="no LC_ALL, no LANG: children must not find an LC_CTYPE that the reference's children do not have"),
+    Scenario(name="env_exported_names_of_script_variables", stdin=_answers("", "", "", "", "2", "1,3", "", "7", "yes"),
+             env={"tmp": "t", "networks": "nn", "packages": "pp", "foundKey": "fk", "countNetwork": "99", "values": "vv",
+                  "gotValidInput": "g", "network": "n", "package": "pk", "i": "5", "yn": "q", "line": "l", "master": "m",
+                  "f": "ff", "node": "nd", "cRetVal": "c", "tmp_ValidatedInput": "tv", "publicNetworkLocation": "9"},
+             curl_seq=[_STARTING],
+             note="the operator's shell happens to export names the script uses: assignments to them stay exported, a "
+                  "`local` takes over the export attribute (children of the function see the local value), what a $(...) "
+                  "assigns is gone after it, and `triton` inside getNetworkIDs' loop finds the current index in `network`"),
     Scenario(name="env_own_switches_do_not_leak", stdin=BLANK8 + YES,
              env={"TK8S_PROGRAM_": "1", "KUBERNETES_TK8S": "kept"},
              note="variables that merely look like the replacement's own switches pass through to terraform/ansible"),

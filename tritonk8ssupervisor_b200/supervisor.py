@@ -35,6 +35,7 @@ Function-by-function correspondence (reference file:line):
 """
 from __future__ import annotations
 
+import contextlib
 import os
 import re
 import shutil
@@ -94,6 +95,7 @@ class Supervisor:
         self._shell_bookkeeping()
         self._tables: Dict[tuple, str] = {}
         self._lineno = 0
+        self._scopes: List[Dict[str, tuple]] = []
         self._evaluator = Evaluator(self._arith_get, self.v.__setitem__, errexit=True)   # setup.sh:3
 
     # ------------------------------------------------------------------
@@ -123,6 +125,56 @@ class Supervisor:
         if "OLDPWD" in env and not os.path.isdir(env["OLDPWD"]):
             del env["OLDPWD"]
             self.v.pop("OLDPWD", None)
+
+    # ------------------------------------------------------------------
+    # `local`: a function's local variable shadows a global of the same name --
+    # including an exported one, which the function's children then do not see --
+    # until the function returns.  A `$(...)` subshell is the same thing seen from
+    # outside: what it assigns is gone afterwards.
+    # ------------------------------------------------------------------
+    @contextlib.contextmanager
+    def scope(self):
+        frame: Dict[str, tuple] = {}
+        self._scopes.append(frame)
+        try:
+            yield
+        finally:
+            self._scopes.pop()
+            env = self.rt.env
+            for name, (had_v, old_v, had_env, old_env) in frame.items():
+                if had_v:
+                    dict.__setitem__(self.v, name, old_v)
+                else:
+                    self.v.pop(name, None)
+                if had_env:
+                    env[name] = old_env
+                else:
+                    env.pop(name, None)
+
+    def _remember(self, name: str) -> None:
+        frame = self._scopes[-1]
+        if name not in frame:
+            env = self.rt.env
+            frame[name] = (name in self.v, self.v.get(name), name in env, env.get(name))
+
+    def local(self, name: str, value: Optional[str] = None) -> None:
+        """``local name[=value]`` in the innermost scope.  The new variable takes
+        over the export attribute of the one it shadows, so children of the
+        function see the *local* value -- or nothing while it has none."""
+        self._remember(name)
+        if value is None:
+            # unset for the shell; but bash assembles a child's environment from the
+            # *visible* exported variables of every scope, and a value-less local is
+            # not visible: children keep seeing the outer exported value until the
+            # local is assigned (rt.env is left as it is)
+            self.v.pop(name, None)
+        else:
+            self.v[name] = value
+
+    def subshell_set(self, name: str, value: str) -> None:
+        """Assignment inside a ``$(...)``: exported if the variable is, undone when the scope ends."""
+        self._remember(name)
+        self.v[name] = value
 
     def export(self, name: str, value: str) -> None:
         self.v[name] = value
@@ -341,6 +393,12 @@ class Supervisor:
         for name in ("SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID"):
             self.append_line("config", '%s="%s"' % (name, v.get(name, "")))
 
+        with self.scope():
+            self.local("foundKey", "false")           # setup.sh:215
+            self._find_key()
+
+    def _find_key(self) -> None:
+        rt, v = self.rt, self.v
         key_id = v.get("SDC_KEY_ID", "")
         found = False
         for f in self.args_of(self._ls_ssh_dir()):
@@ -362,6 +420,7 @@ class Supervisor:
                         found = True
             if found:
                 self.append_line("config", 'SDC_KEY="~/.ssh/%s"' % stem)
+                v["foundKey"] = "true"
                 break
         if not found:
             self.echo("error: couldn't find the ssh key associated with fingerprint %s in ~/.ssh/ directory..." % key_id)
@@ -423,9 +482,11 @@ class Supervisor:
     def _print_menu(self, rows: str, default_prefix: Optional[str], loop_var: str) -> Tuple[int, int]:
         """Numbered menu; returns (row count, 1-based position of the default row)."""
         count, default_at = 0, 1
+        self.v["tmp"] = "0"
         for row in self.args_of(rows):
             self.v[loop_var] = row
             count += 1
+            self.v["tmp"] = str(count)
             shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.rt.root), r"=", "  ", count=0))
             self.rt.out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]))
             if default_prefix is not None and row.startswith(default_prefix):
@@ -435,18 +496,30 @@ class Supervisor:
     def _prompt_validated(self, message: str, var: str, ok: Callable[[str], bool], errors: List[str],
                           lineno: int) -> None:
         default = self.unq(self.v[var])  # evaluated once per attempt in the reference; it cannot change
+        self.v["gotValidInput"] = "false"
         while True:
-            answer = self.get_argument(message, default, lineno)
+            answer = self.v["tmp_ValidatedInput"] = self.get_argument(message, default, lineno)
             if ok(answer):
+                self.v["gotValidInput"] = "true"
                 self.v[var] = answer
                 return
             for line in errors:
                 self.echo(line)
 
     def get_config_from_user(self) -> None:
+        with self.scope():
+            self._get_config_from_user()
+
+    def _get_config_from_user(self) -> None:
         v = self.v
+        # `local networks=$(...)`: the substitution runs before the local exists
         networks = self._menu_rows(TRITON_NETWORKS, kvm_only=False)
+        self.local("networks", networks)
         packages = self._menu_rows(TRITON_PACKAGES, kvm_only=True)
+        self.local("packages", packages)
+        self.local("tmp", "0")
+        self.local("gotValidInput", "false")
+        self.local("tmp_ValidatedInput")
 
         self.echo(DASHES)
         v["KUBERNETES_NAME"] = self.get_argument("Name your Kubernetes environment:", self.unq(v["KUBERNETES_NAME"]), 265)
@@ -476,6 +549,8 @@ class Supervisor:
             ["error: Enter a valid value (number between 1-9) or leave blank to use the default."], 300)
 
         public_at = 1
+        self.local("publicNetworkLocation", "1")      # setup.sh:311-312
+        self.local("countNetwork")
         for var, message, first in (
                 ("RANCHER_MASTER_NETWORKS", "What networks should the master be a part of, provide comma separated values:", True),
                 ("KUBERNETES_NODE_NETWORKS", "What networks should the nodes be a part of, provide comma separated values:", False)):
@@ -485,13 +560,17 @@ class Supervisor:
             count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None, "network")
             if first:
                 public_at = at
+                v["publicNetworkLocation"], v["countNetwork"] = str(at), str(count)
             if v[var] == "":
                 v[var] = self.network_ids(self.args_of(str(public_at)))
             self._prompt_index_list(var, message, count, lineno)
 
         self.echo(DASHES)
         self.echo("From the packages below:")
+        self.local("packageLocation", "1")            # setup.sh:404-405
+        self.local("countPackages")
         count, package_at = self._print_menu(packages, "k4-highcpu-kvm-7.75G=", "package")
+        v["packageLocation"], v["countPackages"] = str(package_at), str(count)
         if v["HOST_PACKAGE"] == "":
             v["HOST_PACKAGE"] = self.package_id(self.args_of(str(package_at)))
         self._prompt_package(count)
@@ -525,14 +604,18 @@ class Supervisor:
         v = self.v
         errors = ["error: Enter a valid option or leave blank to use the default.",
                   "    Values should be comma separated between 1 and %d." % count]
+        v["gotValidInput"] = "false"
         while True:
             answer = self.get_argument(message, self.unq(v[var]), lineno)
             v[var] = self._normalise_list(v[var])
             answer = v["tmp_" + var] = self._normalise_list(answer)
             shown = sh.echo_unquoted(answer, self.rt.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_LIST_RE)) != "":
+                v["gotValidInput"] = "true"
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
                 bad = self._out_of_range(items, count, "network", lineno + 8)
+                if bad:
+                    v["gotValidInput"] = "false"
                 for _ in range(bad):
                     for line in errors:
                         self.echo(line)
@@ -540,6 +623,7 @@ class Supervisor:
                     v[var] = self.network_ids(self.args_of(answer))
                     return
             elif sh.pattern_match(answer, v[var]):
+                v["gotValidInput"] = "true"
                 return  # the default UUID list was left as it is
             else:
                 for line in errors:
@@ -549,13 +633,17 @@ class Supervisor:
         v = self.v
         errors = ["error: Enter a valid option or leave blank to use the default.",
                   "    Value should be between 1 and %d." % count]
+        v["gotValidInput"] = "false"
         while True:
             answer = v["tmp_HOST_PACKAGE"] = self.get_argument("What KVM package should the master and nodes run on:",
                                                                self.unq(v["HOST_PACKAGE"]), 425)
             shown = sh.echo_unquoted(answer, self.rt.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_RE)) != "":
+                v["gotValidInput"] = "true"
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
                 bad = self._out_of_range(items, count, "package", 431)
+                if bad:
+                    v["gotValidInput"] = "false"
                 for _ in range(bad):
                     for line in errors:
                         self.echo(line)
@@ -564,6 +652,7 @@ class Supervisor:
                     self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]))
                     return
             elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"])):
+                v["gotValidInput"] = "true"
                 return
             else:
                 for line in errors:
@@ -577,12 +666,17 @@ class Supervisor:
         rows are sorted *raw* here but after the blank->'=' rewrite in the menu
         (setup.sh:257 vs :536), which is the ordering hazard of SURVEY.md §7.4."""
         arg1 = args[0] if args else ""
-        values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
-        acc = ""
-        for index in self.args_of(values):
-            text = self._triton_table(TRITON_NETWORKS, 536)
-            rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
-            acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
+        with self.scope():                            # runs inside $(...): its assignments do not outlive it
+            values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
+            self.subshell_set("values", values)
+            self.local("networks")
+            acc = ""
+            for index in self.args_of(values):
+                self.subshell_set("network", index)   # what `triton` finds in its environment if `network` is exported
+                text = self._triton_table(TRITON_NETWORKS, 536)
+                rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
+                acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
+                self.v["networks"] = acc
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
         return sh.cmdsubst(tx.sed_sub(t, r"^(.*),$", r"\1"))
 

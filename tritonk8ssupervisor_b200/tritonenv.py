@@ -23,6 +23,18 @@ class TritonEnvError(ValueError):
     pass
 
 
+#: variables that change how bash reads the *rest of the script* (field splitting,
+#: globbing, locale of its pattern matching and of sort/grep/sed).  `eval` would let
+#: `triton env` set them; the path here is written for their default values.
+SHELL_BEHAVIOUR = frozenset(["IFS", "GLOBIGNORE", "POSIXLY_CORRECT", "BASH_COMPAT", "EXECIGNORE", "FUNCNEST",
+                             "LC_ALL", "LC_COLLATE", "LC_CTYPE", "LANG"])
+
+
+def _guard(name: str) -> None:
+    if name in SHELL_BEHAVIOUR:
+        raise TritonEnvError("refusing to let `triton env` output change %s: it alters how the rest of the script is read" % name)
+
+
 class _Var:
     """``$NAME`` / ``${NAME}`` waiting for its value; ``quoted``: inside double quotes."""
 
@@ -227,6 +239,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                 if parsed is None:
                     raise TritonEnvError("not a valid identifier in `triton env` output: %r" % _show(w))
                 name, value = parsed
+                _guard(name)
                 if value is not None:
                     shell_vars[name] = value
                 if name in shell_vars:
@@ -234,6 +247,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
         elif head == "unset":
             for w in words[1:]:
                 name = plain(w)
+                _guard(name)
                 shell_vars.pop(name, None)
                 env.pop(name, None)
         else:
@@ -241,6 +255,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
             if parsed is None or parsed[1] is None:
                 raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(_show(w) for w in words))
             name, value = parsed
+            _guard(name)
             shell_vars[name] = value
             if name in env:
                 env[name] = value
