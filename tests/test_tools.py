@@ -74,3 +74,30 @@ def test_launcher_script_is_the_same_program():
     expected, got = rp.replay(golden_for(CONFIGS[1]), argv=[launcher],
                               extra_env={"PYTHONDONTWRITEBYTECODE": "1", "TK8S_PROGRAM": "<PROGRAM>"})
     assert expected.diff(got) == []
+
+
+def test_inprocess_clock_is_opt_in():
+    """Default: `sleep`/`date +%s` are child processes from PATH, as in the reference
+    (setup.sh:36,41,46,63,64) -- that is what every golden replays.  TK8S_INPROCESS_CLOCK=1
+    removes exactly those entries from the trace and changes nothing else; the switch
+    itself does not reach the tools."""
+    import time
+    from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS
+    from tritonk8ssupervisor_b200.conformance.harness import golden_for
+    doc = golden_for(CONFIGS[0])
+    t0 = time.time()
+    want, got = rp.replay(doc, extra_env=dict(rp.REPLACEMENT_ENV, TK8S_INPROCESS_CLOCK="1"))
+    assert time.time() - t0 >= 6            # three real `sleep 2`s plus the wait loop's seconds
+    assert (got.stdout.replace(".", ""), got.stderr, got.exit_status, got.files) == (want.stdout.replace(".", ""), want.stderr, want.exit_status, want.files)
+
+    def tools(calls):
+        out, keep = [], True
+        for c in calls:
+            if not c.startswith("  "):
+                keep = c.split("|")[0] not in ("sleep", "date")
+            if keep:
+                out.append(c)
+        return out
+    assert got.calls == tools(got.calls) == tools(want.calls)
+    assert len(want.calls) > len(got.calls)
+    assert not any("TK8S_INPROCESS_CLOCK" in c for c in got.calls)

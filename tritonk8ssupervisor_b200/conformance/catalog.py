@@ -12,7 +12,7 @@ from __future__ import annotations
 import dataclasses
 from typing import Dict, List
 
-from .scenario import DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario, triton_table
+from .scenario import DEFAULT_KEY_ID, DOC_NETWORKS, DOC_PACKAGES, NON_KVM_PACKAGES, Scenario, triton_env_text, triton_table
 
 YES = "yes\n"
 BLANK8 = "\n" * 8
@@ -342,6 +342,10 @@ EDGE += [
              triton_env='PREFIX=https://$HOME\nexport SDC_URL="${PREFIX}/x"\nexport SDC_ACCOUNT=$UNSET_ONE"acct"\n'
                         'export SDC_KEY_ID="%s"\nexport TRITON_PROFILE=~/profile:~\n' % DEFAULT_KEY_ID,
              note="$NAME, ${NAME} and ~ in assignments execute nothing and are expanded as bash's eval expands them"),
+    Scenario(name="triton_env_exports_names_without_values", stdin=_answers("", "", "", "", "2", "1,2", "", "", "yes"),
+             triton_env=triton_env_text() + "export i network\nexport master yn\nunset yn\n",
+             note="`export NAME` before NAME has a value: it is exported the moment the script assigns it (the loop "
+                  "counter i reaches terraform as i=3); unset takes the attribute away again"),
     # --- children that read the stdin they inherit ------------------------------------
     Scenario(name="stdin_taken_by_ssh_keygen", stdin="eaten by ssh-keygen\n" + BLANK8 + YES, stdin_eaters={"ssh-keygen--E": 1},
              note="stdin is read a byte at a time, so a child sees exactly what is left: here the first line"),

@@ -70,10 +70,13 @@ class _ShellVars(dict):
     def __init__(self, env: Dict[str, str]):
         super().__init__(env)
         self._env = env
+        #: names given the export attribute before they had a value (`export NAME`)
+        self.export_when_set: set = set()
 
     def __setitem__(self, key: str, value: str) -> None:
         super().__setitem__(key, value)
-        if key in self._env:
+        if key in self._env or key in self.export_when_set:
+            self.export_when_set.discard(key)
             self._env[key] = value
 
 
@@ -141,7 +144,9 @@ class Supervisor:
         finally:
             self._scopes.pop()
             env = self.rt.env
-            for name, (had_v, old_v, had_env, old_env) in frame.items():
+            for name, (had_v, old_v, had_env, old_env, was_pending) in frame.items():
+                if was_pending:
+                    self.v.export_when_set.add(name)
                 if had_v:
                     dict.__setitem__(self.v, name, old_v)
                 else:
@@ -155,7 +160,7 @@ class Supervisor:
         frame = self._scopes[-1]
         if name not in frame:
             env = self.rt.env
-            frame[name] = (name in self.v, self.v.get(name), name in env, env.get(name))
+            frame[name] = (name in self.v, self.v.get(name), name in env, env.get(name), name in self.v.export_when_set)
 
     def local(self, name: str, value: Optional[str] = None) -> None:
         """``local name[=value]`` in the innermost scope.  The new variable takes

@@ -231,6 +231,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
             raise TritonEnvError("refusing to expand a parameter outside an assignment in `triton env` output")
         return "".join(p[0] for p in word)        # type: ignore[index]
 
+    pending = getattr(shell_vars, "export_when_set", None)
     for words in _split_commands(text):
         head = plain(words[0]) if not any(isinstance(p, _Var) for p in words[0]) else None
         if head == "export":
@@ -244,12 +245,16 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                     shell_vars[name] = value
                 if name in shell_vars:
                     env[name] = shell_vars[name]
+                elif pending is not None:
+                    pending.add(name)           # `export NAME` before NAME has a value: exported once it gets one
         elif head == "unset":
             for w in words[1:]:
                 name = plain(w)
                 _guard(name)
                 shell_vars.pop(name, None)
                 env.pop(name, None)
+                if pending is not None:
+                    pending.discard(name)
         else:
             parsed = _assignment(words[0], shell_vars, tilde_home) if len(words) == 1 else None
             if parsed is None or parsed[1] is None:
