@@ -186,7 +186,20 @@ def _read_in_blocks(self, prompt):
     return bashsem.read_builtin(nb)
 
 
+def _clean_shrugs_off_rm_failures(orig):
+    def _clean(self):
+        try:
+            orig(self)
+        except supervisor.ScriptExit:
+            pass
+    return _clean
+
+
 MUTANTS_2 = [
+    ("clean carries on when rm could not remove something", supervisor.Supervisor, "_clean",
+     _clean_shrugs_off_rm_failures(supervisor.Supervisor._clean), {"ws_clean_retry_is_a_directory", "clean_keygen_R_fails"}),
+    ("a directory is a file that cannot be read, says sed", supervisor.os.path, "isdir", lambda p: False,
+     {"ws_cfg_is_a_directory", "ws_clean_cfg_is_a_directory"}),
     ("a clock reading that is not a number is skipped", supervisor.Supervisor, "arith_eval",
      _arith_digits_only(supervisor.Supervisor.arith_eval),
      {"wait_clock_word", "wait_clock_negative", "wait_clock_empty", "wait_clock_two_words",

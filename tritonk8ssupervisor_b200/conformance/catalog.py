@@ -371,6 +371,25 @@ EDGE += [
              pre_symlinks={"ansible/ansible.cfg": "real.cfg", "terraform/rancher.tf": "../elsewhere/keep", "tmp/link": "../elsewhere",
                            "terraform/.terraform": "../elsewhere"},
              note="rm -rf removes links, never what they point to"),
+    # --- odd workspaces: a directory or a dead link where the script expects a file -----------
+    Scenario(name="ws_clean_retry_is_a_directory", args=["-c"], stdin="yes\n",
+             pre_files={"ansible/a.retry/keep": "k\n", "ansible/b.retry": "h\n", "ansible/ansible.cfg.tmp/keep": "k\n", "config": "x\n"},
+             note="rm -f goes through all its arguments, complains on the script's stdout (2>&1 >> /dev/null) and fails at "
+                  "the end: errexit, ./config survives"),
+    Scenario(name="ws_cfg_is_a_directory", stdin=BLANK8 + YES, pre_remove=["ansible/ansible.cfg"], pre_files={"ansible/ansible.cfg/keep": "k\n"},
+             note="sed opens a directory and fails on read ('read error on', not 'can't read'); tmp.cfg stays behind, the run goes on"),
+    Scenario(name="ws_clean_cfg_is_a_directory", args=["-c"], stdin="yes\n", pre_remove=["ansible/ansible.cfg"],
+             pre_files={"ansible/ansible.cfg/keep": "k\n"}, note="the same at setup.sh:511, where sed is given the longer path"),
+    Scenario(name="ws_config_tmp_is_a_dead_link", stdin=BLANK8 + YES, pre_symlinks={"config.tmp": "/nonexistent/x"},
+             note="grep ... > config.tmp: the redirection fails first (message names line 544), errexit"),
+    Scenario(name="ws_config_tmp_is_a_directory", stdin=BLANK8 + YES, pre_files={"config.tmp/keep": "k\n"},
+             note="... and so it does on a directory"),
+    Scenario(name="ws_masters_ip_is_a_directory", stdin=BLANK8 + YES, terraform_no_ips=True,
+             pre_files={"terraform/masters.ip/keep": "k\n", "terraform/hosts.ip": "10.0.1.1\n"},
+             note="[[ -e ]] is satisfied by a directory; `cat terraform/masters.ip >> ansible/hosts` is not: cat's message, errexit"),
+    Scenario(name="ws_clean_ip_files_are_directories", args=["-c"], stdin="yes\n", known_hosts="h\n",
+             pre_files={"terraform/masters.ip/keep": "k\n", "terraform/hosts.ip/keep": "k\n"},
+             note="clean: `cat masters.ip 2>/dev/null` before the prompt fails silently and errexit ends it there"),
     # --- bytes ------------------------------------------------------------------------------
     Scenario(name="text_70kb_line", stdin=_answers("x" * 70000, "", "", "", "", "", "", "", "yes"),
              note="a 70 KB answer: no line-length limit anywhere on the path"),

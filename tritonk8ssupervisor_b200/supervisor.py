@@ -395,8 +395,8 @@ class Supervisor:
         except TritonEnvError as exc:
             rt.err("%s: %s\n" % (self.program, exc))
             raise ScriptExit(2)
-        for name in ("SDC_URL", "SDC_ACCOUNT", "SDC_KEY_ID"):
-            self.append_line("config", '%s="%s"' % (name, v.get(name, "")))
+        for lineno, name in ((211, "SDC_URL"), (212, "SDC_ACCOUNT"), (213, "SDC_KEY_ID")):
+            self.append_line("config", '%s="%s"' % (name, v.get(name, "")), lineno)
 
         with self.scope():
             self.local("foundKey", "false")           # setup.sh:215
@@ -414,9 +414,11 @@ class Supervisor:
             key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], rt.root)
             _, out = rt.run(["ssh-keygen", "-E", "md5", "-lf"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
             fp = sh.cmdsubst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""))
+            matched_at = 218
             if fp == key_id:
                 found = True
             else:
+                matched_at = 225
                 # ssh-keygen too old for -E prints MD5 by default (setup.sh:222-229)
                 _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
                 if sh.cmdsubst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256")) == "":
@@ -424,7 +426,7 @@ class Supervisor:
                     if sh.cmdsubst(tx.awk_print_field(out, 2)) == key_id:
                         found = True
             if found:
-                self.append_line("config", 'SDC_KEY="~/.ssh/%s"' % stem)
+                self.append_line("config", 'SDC_KEY="~/.ssh/%s"' % stem, matched_at)
                 v["foundKey"] = "true"
                 break
         if not found:
@@ -433,11 +435,13 @@ class Supervisor:
             self.echo("    To confirm your profile is set up, try `triton info`.")
             self.clean_runner()
             raise ScriptExit(1)
-        self.append_line("config", "")
+        self.append_line("config", "", 238)
 
     def _ls_ssh_dir(self) -> str:
         """``$(ls ~/.ssh)``: names one per line, C collation, dot files hidden."""
         d = self.tilde("~/.ssh")
+        if os.path.exists(d) and not os.path.isdir(d):
+            return d                                  # `ls FILE` prints the name it was given
         try:
             names = os.listdir(d)
         except OSError as exc:
@@ -743,11 +747,11 @@ class Supervisor:
     # ------------------------------------------------------------------
     def set_config_to_file(self) -> None:
         v = self.v
-        for name in ("RANCHER_MASTER_NETWORKS", "KUBERNETES_NODE_NETWORKS", "KUBERNETES_NUMBER_OF_NODES"):
-            self.append_line("config", "%s=%s" % (name, v[name]))
-        for name in ("KUBERNETES_NAME", "KUBERNETES_DESCRIPTION", "RANCHER_MASTER_HOSTNAME",
-                     "KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "HOST_PACKAGE"):
-            self.append_line("config", '%s="%s"' % (name, v[name]))
+        for k, name in enumerate(("RANCHER_MASTER_NETWORKS", "KUBERNETES_NODE_NETWORKS", "KUBERNETES_NUMBER_OF_NODES")):
+            self.append_line("config", "%s=%s" % (name, v[name]), 200 + k)
+        for k, name in enumerate(("KUBERNETES_NAME", "KUBERNETES_DESCRIPTION", "RANCHER_MASTER_HOSTNAME",
+                                  "KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "HOST_PACKAGE")):
+            self.append_line("config", '%s="%s"' % (name, v[name]), 203 + k)
 
     # ------------------------------------------------------------------
     # a9  exportVars  (setup.sh:543-549)
@@ -756,8 +760,19 @@ class Supervisor:
         """Every non-blank line of ./config is exported *verbatim*: values keep
         their literal double quotes from here on, and each line
         goes through ``read`` once more (backslashes processed again)."""
-        text = tx.grep(self.rt.read_text("config"), r"^$", invert=True)
+        # grep -v "^$" config > config.tmp: the redirection comes first, then grep's own troubles
+        try:
+            self.rt.write_text("config.tmp", "")
+        except OSError as exc:
+            self._redirect_failed("config.tmp", exc, 544)
+        try:
+            text = tx.grep(self.rt.read_text("config"), r"^$", invert=True)
+        except OSError as exc:
+            self.rt.err("grep: config: %s\n" % exc.strerror)
+            raise ScriptExit(2)
         self.rt.write_text("config.tmp", text)  # stays behind if an export fails (errexit)
+        if text == "":
+            raise ScriptExit(1)                 # grep selected nothing: status 1, errexit
         data = sh.to_bytes(text)
         pos = 0
 
@@ -844,8 +859,10 @@ class Supervisor:
                 '    package = "%s"' % self.unq(v.get("HOST_PACKAGE", "")),
                 "}",
             ]
-            for line in block:
-                self.append_line(rel, line)
+            first = 164 if kind == "master" else 176
+            for k, line in enumerate(block):
+                # the commented-out image line (setup.sh:170,182) sits between the key and the package line
+                self.append_line(rel, line, first + k + (1 if k >= 6 else 0))
             return
         if kind == "provider":
             block = [
@@ -860,8 +877,8 @@ class Supervisor:
                 self.rt.write_text(rel, sh.echo_builtin([block[0]]))
             except OSError as exc:
                 self._redirect_failed(rel, exc, 188)
-            for line in block[1:]:
-                self.append_line(rel, line)
+            for k, line in enumerate(block[1:]):
+                self.append_line(rel, line, 189 + k)
             return
         self.echo("error: problem updating terraform configuration...")
         raise ScriptExit(1)
@@ -881,25 +898,43 @@ class Supervisor:
         if os.path.lexists(rt.path(hosts)):
             os.remove(rt.path(hosts))
         self.append_line(hosts, "[MASTER]", 123)
-        rt.append_text(hosts, rt.read_text("terraform/masters.ip"))
-        self.append_line(hosts, "[HOST]")
-        rt.append_text(hosts, rt.read_text("terraform/hosts.ip"))
+        self._cat_append("terraform/masters.ip", hosts, 124)
+        self.append_line(hosts, "[HOST]", 125)
+        self._cat_append("terraform/hosts.ip", hosts, 126)
         self.echo("    created: ansible/hosts")
 
         vars_yml = "ansible/roles/ranchermaster/vars/vars.yml"
-        master = v["master"] = sh.cmdsubst(tx.tail_1(rt.read_text("terraform/masters.ip")))
+        try:
+            last = tx.tail_1(rt.read_text("terraform/masters.ip"))
+        except OSError as exc:
+            rt.err("tail: error reading 'terraform/masters.ip': %s\n" % exc.strerror)
+            raise ScriptExit(1)                 # master=$(tail ...): the assignment has tail's status, errexit
+        master = v["master"] = sh.cmdsubst(last)
         try:
             rt.write_text(vars_yml, sh.echo_builtin(["master: %s" % master]))
         except OSError as exc:
             self._redirect_failed(vars_yml, exc, 129)
-        self.append_line(vars_yml, 'kubernetes_name: "%s"' % self.unq(v.get("KUBERNETES_NAME", "")))
-        self.append_line(vars_yml, 'kubernetes_description: "%s"' % self.unq(v.get("KUBERNETES_DESCRIPTION", "")))
+        self.append_line(vars_yml, 'kubernetes_name: "%s"' % self.unq(v.get("KUBERNETES_NAME", "")), 130)
+        self.append_line(vars_yml, 'kubernetes_description: "%s"' % self.unq(v.get("KUBERNETES_DESCRIPTION", "")), 131)
 
         self.cd("ansible")
         self._rewrite_private_key_file("ansible/ansible.cfg", "ansible/tmp.cfg", ";", self.unq(v.get("SDC_KEY", "")),
                                        shown_src="ansible.cfg")
         self.cd("..")
         self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml")
+
+    def _cat_append(self, src: str, dst: str, lineno: int) -> None:
+        """``cat src >> dst`` under errexit."""
+        try:
+            self.rt.append_text(dst, "")        # the redirection is set up before cat runs
+        except OSError as exc:
+            self._redirect_failed(dst, exc, lineno)
+        try:
+            text = self.rt.read_text(src)
+        except OSError as exc:
+            self.rt.err("cat: %s: %s\n" % (src, exc.strerror))
+            raise ScriptExit(1)
+        self.rt.append_text(dst, text)
 
     def _rewrite_private_key_file(self, cfg: str, tmp: str, delim: str, value: str, shown_src: str,
                                   lineno: int = 133) -> None:
@@ -922,12 +957,27 @@ class Supervisor:
             rt.err(res.error)        # a program sed rejects is reported before it opens any input
             return
         if not readable:
-            rt.err("sed: can't read %s: %s\n" % (shown_src, why))
+            if os.path.isdir(rt.path(cfg)):
+                rt.err("sed: read error on %s: %s\n" % (shown_src, why))     # a directory opens fine and fails on read
+            else:
+                rt.err("sed: can't read %s: %s\n" % (shown_src, why))
             return
         for name, content in res.wfiles.items():     # a `w` flag smuggled in through VALUE writes next to the input
             rt.write_text(os.path.join(os.path.dirname(tmp), name), content)
         rt.write_text(tmp, res.output)
-        os.replace(rt.path(tmp), rt.path(cfg))
+        # mv tmp cfg: into cfg when that is a directory; the last command of an && list is subject to errexit
+        dest, shown_dest = rt.path(cfg), shown_src
+        if os.path.isdir(dest):
+            dest = os.path.join(dest, os.path.basename(tmp))
+            shown_dest = "%s/%s" % (shown_src, os.path.basename(tmp))
+            if os.path.isdir(dest) and not os.path.islink(dest):
+                rt.err("mv: cannot overwrite directory '%s' with non-directory\n" % shown_dest)
+                raise ScriptExit(1)
+        try:
+            os.replace(rt.path(tmp), dest)
+        except OSError as exc:
+            rt.err("mv: cannot move '%s' to '%s': %s\n" % (os.path.basename(tmp) if lineno == 133 else tmp, shown_dest, exc.strerror))
+            raise ScriptExit(1)
 
     # ------------------------------------------------------------------
     # runAnsible  (setup.sh:111-115)
@@ -1049,7 +1099,13 @@ class Supervisor:
             self.cd("..")
         if (rt.exists("terraform/hosts.ip") and rt.exists("terraform/masters.ip")
                 and os.path.exists(self.tilde("~/.ssh/known_hosts"))):
-            recorded = sh.cmdsubst(rt.read_text("terraform/hosts.ip") + rt.read_text("terraform/masters.ip"))
+            recorded = ""
+            for rel in ("terraform/hosts.ip", "terraform/masters.ip"):      # $(cat a b) in a `for` list: errors only cost a message
+                try:
+                    recorded += rt.read_text(rel)
+                except OSError as exc:
+                    rt.err("cat: %s: %s\n" % (rel, exc.strerror))
+            recorded = sh.cmdsubst(recorded)
             for host_key in self.args_of(recorded):
                 self.v["host_key"] = host_key
                 # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped
@@ -1061,12 +1117,18 @@ class Supervisor:
             for rel in sh.glob_word(pattern, rt.root):
                 _rm_rf(rt.path(rel))
         self._rewrite_private_key_file("ansible/ansible.cfg", "tmp", "~", "", shown_src="ansible/ansible.cfg", lineno=511)
-        for rel in ["ansible/hosts", "ansible/ansible.cfg.tmp"] + sh.glob_word("ansible/*retry", rt.root):
+        # rm -f ansible/hosts ansible/*retry ansible/ansible.cfg.tmp 2>&1 >> /dev/null: rm goes through
+        # all its arguments, complains on the script's *stdout* (2>&1 comes first) and fails at the end
+        failed = False
+        for rel in ["ansible/hosts"] + sh.glob_word("ansible/*retry", rt.root) + ["ansible/ansible.cfg.tmp"]:
             p = rt.path(rel)
-            if os.path.isfile(p) or os.path.islink(p):
+            if os.path.isdir(p) and not os.path.islink(p):
+                rt.out("rm: cannot remove '%s': Is a directory\n" % rel)
+                failed = True
+            elif os.path.lexists(p):
                 os.remove(p)
-            elif os.path.isdir(p):
-                rt.err("rm: cannot remove '%s': Is a directory\n" % rel)
+        if failed:
+            raise ScriptExit(1)
         _rm_rf(rt.path("config"))
         for rel in sh.glob_word("tmp/*", rt.root):
             _rm_rf(rt.path(rel))
