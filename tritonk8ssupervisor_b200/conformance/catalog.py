@@ -384,6 +384,12 @@ EDGE += [
              note="grep ... > config.tmp: the redirection fails first (message names line 544), errexit"),
     Scenario(name="ws_config_tmp_is_a_directory", stdin=BLANK8 + YES, pre_files={"config.tmp/keep": "k\n"},
              note="... and so it does on a directory"),
+    Scenario(name="ws_config_tmp_links_to_dev_null", stdin=BLANK8 + YES, pre_symlinks={"config.tmp": "/dev/null"},
+             note="exportVars reads back what config.tmp holds: nothing. No variable is exported, values keep the shapes they "
+                  "had as plain shell variables (no literal quotes), SDC_KEY is not set at all"),
+    Scenario(name="ws_tmp_cfg_links_to_ansible_cfg", stdin=BLANK8 + YES, pre_symlinks={"ansible/tmp.cfg": "ansible.cfg"},
+             note="`sed ... ansible.cfg > tmp.cfg` empties ansible.cfg through the link before sed reads it, and mv refuses: "
+                  "'are the same file', errexit"),
     Scenario(name="ws_masters_ip_is_a_directory", stdin=BLANK8 + YES, terraform_no_ips=True,
              pre_files={"terraform/masters.ip/keep": "k\n", "terraform/hosts.ip": "10.0.1.1\n"},
              note="[[ -e ]] is satisfied by a directory; `cat terraform/masters.ip >> ansible/hosts` is not: cat's message, errexit"),

@@ -773,7 +773,8 @@ class Supervisor:
         self.rt.write_text("config.tmp", text)  # stays behind if an export fails (errexit)
         if text == "":
             raise ScriptExit(1)                 # grep selected nothing: status 1, errexit
-        data = sh.to_bytes(text)
+        # done <config.tmp: what is read back is what the file holds (a link to /dev/null holds nothing)
+        data = sh.to_bytes(self.rt.read_text("config.tmp"))
         pos = 0
 
         def next_byte() -> Optional[int]:
@@ -967,6 +968,14 @@ class Supervisor:
         rt.write_text(tmp, res.output)
         # mv tmp cfg: into cfg when that is a directory; the last command of an && list is subject to errexit
         dest, shown_dest = rt.path(cfg), shown_src
+        shown_tmp = os.path.basename(tmp) if lineno == 133 else tmp
+        try:
+            same = os.path.samefile(rt.path(tmp), dest)
+        except OSError:
+            same = False
+        if same:                                     # tmp is a link to cfg: sed has just emptied it through the link
+            rt.err("mv: '%s' and '%s' are the same file\n" % (shown_tmp, shown_dest))
+            raise ScriptExit(1)
         if os.path.isdir(dest):
             dest = os.path.join(dest, os.path.basename(tmp))
             shown_dest = "%s/%s" % (shown_src, os.path.basename(tmp))
@@ -976,7 +985,7 @@ class Supervisor:
         try:
             os.replace(rt.path(tmp), dest)
         except OSError as exc:
-            rt.err("mv: cannot move '%s' to '%s': %s\n" % (os.path.basename(tmp) if lineno == 133 else tmp, shown_dest, exc.strerror))
+            rt.err("mv: cannot move '%s' to '%s': %s\n" % (shown_tmp, shown_dest, exc.strerror))
             raise ScriptExit(1)
 
     # ------------------------------------------------------------------
