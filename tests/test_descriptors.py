@@ -1,0 +1,44 @@
+"""Standard descriptors that are closed or cannot be written: the program must
+behave like the bash script, not die with a traceback.  Expected values are
+what the reference does (compared live where a reference tree is available)."""
+import subprocess
+
+import pytest
+
+from tritonk8ssupervisor_b200.conformance import replay as rp
+from tritonk8ssupervisor_b200.conformance.catalog import CONFIGS
+from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE
+from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox
+
+CASES = {
+    # redirection applied to the program : (exit status, stderr, last line of stdout)
+    "stdout closed": (">&-", 1, "./setup.sh: line 264: echo: write error: Bad file descriptor\n", None),
+    "stdout on a full device": ("> /dev/full", 1, "./setup.sh: line 264: echo: write error: No space left on device\n", None),
+    "stderr closed": ("2>&-", 0, "", "    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!"),
+    "stdin from /dev/null": ("< /dev/null", 1, "", "WARN: Make sure that the nodes and master are part of networks that can communicate "
+                                                     "with each other and this system from which the setup is running."),
+}
+
+
+def _run(argv, env, workspace_src, redirection):
+    with Sandbox(workspace_src, CONFIGS[0]) as sbx:
+        p = subprocess.run(["sh", "-c", 'exec "$@" ' + redirection, "sh"] + list(argv), cwd=sbx.workspace,
+                           input=None if "<" in redirection else CONFIGS[0].stdin.encode(),
+                           stdin=subprocess.DEVNULL if "<" in redirection else None,
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=sbx.env(env), timeout=60)
+        out = p.stdout.decode().splitlines()
+        return p.returncode, p.stderr.decode().replace(sbx.tmp, "<SBX>"), (out[-1] if out else None)
+
+
+@pytest.mark.parametrize("label", sorted(CASES))
+def test_odd_descriptors(label):
+    redirection, status, stderr, last = CASES[label]
+    got = _run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, WORKSPACE_TEMPLATE, redirection)
+    assert got == (status, stderr, last)
+    assert "Traceback" not in got[1]
+
+
+@pytest.mark.parametrize("label", sorted(CASES))
+def test_odd_descriptors_same_as_reference(ref_root, label):
+    redirection = CASES[label][0]
+    assert _run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root, redirection) == _run(["./setup.sh"], None, ref_root, redirection)

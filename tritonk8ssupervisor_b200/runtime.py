@@ -129,7 +129,10 @@ class HostRuntime(Runtime):
         _write_all(self.stdout_fd, bashsem.to_bytes(text))
 
     def err(self, text: str) -> None:
-        _write_all(self.stderr_fd, bashsem.to_bytes(text))
+        try:
+            _write_all(self.stderr_fd, bashsem.to_bytes(text))
+        except OSError:
+            pass                # a diagnostic that cannot be written is lost, as bash's are
 
     def _next_byte(self) -> Optional[int]:
         try:
@@ -146,10 +149,15 @@ class HostRuntime(Runtime):
 
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
             stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
-        out_target = {INHERIT: self.stdout_fd, DEVNULL: subprocess.DEVNULL,
+        # A child inherits our descriptors as they are -- closed ones included (`./setup.sh 2>&-`);
+        # naming 0/1/2 explicitly would make Popen dup them and fail on a closed one.
+        def inherit(fd: int, std: int):
+            return None if fd == std else fd
+        out_target = {INHERIT: inherit(self.stdout_fd, 1), DEVNULL: subprocess.DEVNULL,
                       CAPTURE: subprocess.PIPE}[stdout]
-        err_target = {INHERIT: self.stderr_fd, DEVNULL: subprocess.DEVNULL,
+        err_target = {INHERIT: inherit(self.stderr_fd, 2), DEVNULL: subprocess.DEVNULL,
                       TO_STDOUT: self.stdout_fd}[stderr]
+        in_target = inherit(self.stdin_fd, 0)
         # Ctrl-C goes to the whole foreground process group, the child included.  bash
         # does not act on it while the child runs: it waits for the child to finish
         # whatever it does about the signal (terraform saving its state), and only
@@ -172,7 +180,7 @@ class HostRuntime(Runtime):
                 # bash puts the path of the command it starts into the command's environment as `_`
                 proc = subprocess.Popen(list(argv), executable=exe, cwd=self.path(cwd),
                                         env=child_env(self.env, exe, lone_subst),
-                                        stdin=self.stdin_fd, stdout=out_target, stderr=err_target)
+                                        stdin=in_target, stdout=out_target, stderr=err_target)
             except (FileNotFoundError, PermissionError) as exc:
                 # what bash says; the message follows the command's own redirections
                 missing = isinstance(exc, FileNotFoundError)

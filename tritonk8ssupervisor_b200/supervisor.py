@@ -195,9 +195,20 @@ class Supervisor:
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
     # ------------------------------------------------------------------
-    def echo(self, line: str = "") -> None:
-        """``echo "<line>"`` with a double-quoted argument."""
-        self.rt.out(sh.echo_builtin([line]))
+    def echo(self, line: str = "", lineno: int = 0) -> None:
+        """``echo "<line>"`` with a double-quoted argument (``lineno``: its line in the reference)."""
+        self.write_out(sh.echo_builtin([line]), lineno)
+
+    def write_out(self, text: str, lineno: int = 0) -> None:
+        """An ``echo`` to the script's stdout.  One that cannot be written (stdout
+        closed, disk full) costs bash's message and, under errexit, the run."""
+        try:
+            self.rt.out(text)
+        except BrokenPipeError:
+            raise                               # SIGPIPE has its default action; only an embedding caller gets here
+        except OSError as exc:
+            self.rt.err("%s: echo: write error: %s\n" % (self.at(lineno) if lineno else self.program, exc.strerror))
+            raise ScriptExit(1)
 
     def echo_var(self, value: str) -> str:
         """``$(echo $VALUE)``: unquoted, so field-split and globbed in the workspace."""
@@ -321,8 +332,8 @@ class Supervisor:
             self.clean_runner()
             raise ScriptExit(0)
         if rt.exists("terraform/rancher.tf"):
-            self.echo("error: configuration for a previous run has been found")
-            self.echo("    clean the configuration (./setup -c)")
+            self.echo("error: configuration for a previous run has been found", lineno=15)
+            self.echo("    clean the configuration (./setup -c)", lineno=16)
             raise ScriptExit(0)  # bare `exit` after a successful echo
 
         self.set_var_defaults()
@@ -341,29 +352,29 @@ class Supervisor:
 
         master = self.cat_subst("terraform/masters.ip")
         env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
-        self.echo("")
-        self.echo("Congratulations, your Kubernetes cluster setup has been complete.")
-        self.echo("")
-        self.echo("It will take a few minutes for all the Kubernetes process to start up before you can access Kubernetes Dashboard")
-        self.echo("----> To check what processes/containers are coming up, go to http://%s:8080/env/%s/infra/containers" % (master, env_id))
-        self.echo("    once all these containers are up, you should be able to access Kubernetes by its dashboard or using CLI")
-        self.echo("Waiting on Kubernetes dashboard to come up.")
-        self.echo("")
+        self.echo("", lineno=49)
+        self.echo("Congratulations, your Kubernetes cluster setup has been complete.", lineno=50)
+        self.echo("", lineno=51)
+        self.echo("It will take a few minutes for all the Kubernetes process to start up before you can access Kubernetes Dashboard", lineno=52)
+        self.echo("----> To check what processes/containers are coming up, go to http://%s:8080/env/%s/infra/containers" % (master, env_id), lineno=53)
+        self.echo("    once all these containers are up, you should be able to access Kubernetes by its dashboard or using CLI", lineno=54)
+        self.echo("Waiting on Kubernetes dashboard to come up.", lineno=56)
+        self.echo("", lineno=57)
         self.wait_for_dashboard()
-        self.echo("")
+        self.echo("", lineno=87)
         master = self.cat_subst("terraform/masters.ip")
         env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
-        self.echo("----> Kubernetes dashboard is at http://%s:8080/r/projects/%s/kubernetes-dashboard:9090/" % (master, env_id))
+        self.echo("----> Kubernetes dashboard is at http://%s:8080/r/projects/%s/kubernetes-dashboard:9090/" % (master, env_id), lineno=88)
         master = self.cat_subst("terraform/masters.ip")
         env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
-        self.echo("----> Kubernetes CLI config is at http://%s:8080/env/%s/kubernetes/kubectl" % (master, env_id))
-        self.echo("")
-        self.echo("    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!")
+        self.echo("----> Kubernetes CLI config is at http://%s:8080/env/%s/kubernetes/kubectl" % (master, env_id), lineno=89)
+        self.echo("", lineno=90)
+        self.echo("    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!", lineno=91)
 
     def banner(self, text: str, line: int = 0) -> None:
-        self.echo(RULE)
-        self.echo("### " + text)
-        self.echo(RULE)
+        self.echo(RULE, lineno=line - 3)
+        self.echo("### " + text, lineno=line - 2)
+        self.echo(RULE, lineno=line - 1)
         self.must(self.rt.sleep(2, self.at(line)))
 
     # ------------------------------------------------------------------
@@ -371,7 +382,7 @@ class Supervisor:
     # ------------------------------------------------------------------
     def set_var_defaults(self) -> None:
         if self.rt.exists("config"):
-            self.echo("error: old configuration found")
+            self.echo("error: old configuration found", lineno=242)
             self.clean_runner()
         v = self.v
         v["KUBERNETES_NAME"] = "k8s dev"
@@ -430,9 +441,9 @@ class Supervisor:
                 v["foundKey"] = "true"
                 break
         if not found:
-            self.echo("error: couldn't find the ssh key associated with fingerprint %s in ~/.ssh/ directory..." % key_id)
-            self.echo("    Clean the setup and make sure your triton profile is set up.")
-            self.echo("    To confirm your profile is set up, try `triton info`.")
+            self.echo("error: couldn't find the ssh key associated with fingerprint %s in ~/.ssh/ directory..." % key_id, lineno=232)
+            self.echo("    Clean the setup and make sure your triton profile is set up.", lineno=233)
+            self.echo("    To confirm your profile is set up, try `triton info`.", lineno=234)
             self.clean_runner()
             raise ScriptExit(1)
         self.append_line("config", "", 238)
@@ -497,7 +508,7 @@ class Supervisor:
             count += 1
             self.v["tmp"] = str(count)
             shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.rt.root), r"=", "  ", count=0))
-            self.rt.out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]))
+            self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]), {"network": 316, "package": 409}.get(loop_var, 0))
             if default_prefix is not None and row.startswith(default_prefix):
                 default_at = count
         return count, default_at
@@ -530,27 +541,27 @@ class Supervisor:
         self.local("gotValidInput", "false")
         self.local("tmp_ValidatedInput")
 
-        self.echo(DASHES)
+        self.echo(DASHES, lineno=264)
         v["KUBERNETES_NAME"] = self.get_argument("Name your Kubernetes environment:", self.unq(v["KUBERNETES_NAME"]), 265)
-        self.echo(DASHES)
+        self.echo(DASHES, lineno=266)
         # the description default is whatever the description already holds
         # ("k8s dev" from the defaults), not the name just entered (setup.sh:267-271)
         blank = v["KUBERNETES_DESCRIPTION"] == ""
         descr_default = v["KUBERNETES_NAME"] if blank else v["KUBERNETES_DESCRIPTION"]
         v["KUBERNETES_DESCRIPTION"] = self.get_argument("Describe this Kubernetes environment:", self.unq(descr_default),
                                                         268 if blank else 270)
-        self.echo(DASHES)
+        self.echo(DASHES, lineno=272)
         self._prompt_validated(
             "Hostname of the master:", "RANCHER_MASTER_HOSTNAME", lambda s: HOSTNAME_RE.fullmatch(s) is not None,
             ["error: Enter a valid hostname or leave blank to use the default.",
              "    Must start with a letter and can only include letters and numbers"], 275)
-        self.echo(DASHES)
+        self.echo(DASHES, lineno=284)
         self._prompt_validated(
             "Enter a string to use for appending to hostnames of all the nodes:", "KUBERNETES_NODE_HOSTNAME_BEGINSWITH",
             lambda s: HOSTNAME_RE.fullmatch(s) is not None,
             ["error: Enter a valid value or leave blank to use the default.",
              "    Must start with a letter and can only include letters and numbers"], 287)
-        self.echo(DASHES)
+        self.echo(DASHES, lineno=296)
         # hard limit 1-9: the setup has no HA (setup.sh:296)
         self._prompt_validated(
             "How many nodes should this Kubernetes cluster have:", "KUBERNETES_NUMBER_OF_NODES",
@@ -564,8 +575,8 @@ class Supervisor:
                 ("RANCHER_MASTER_NETWORKS", "What networks should the master be a part of, provide comma separated values:", True),
                 ("KUBERNETES_NODE_NETWORKS", "What networks should the nodes be a part of, provide comma separated values:", False)):
             lineno = 332 if first else 375
-            self.echo(DASHES)
-            self.echo("From the networks below:")
+            self.echo(DASHES, lineno=308 if first else 358)
+            self.echo("From the networks below:", lineno=309 if first else 359)
             count, at = self._print_menu(networks, "Joyent-SDC-Public=" if first else None, "network")
             if first:
                 public_at = at
@@ -574,8 +585,8 @@ class Supervisor:
                 v[var] = self.network_ids(self.args_of(str(public_at)))
             self._prompt_index_list(var, message, count, lineno)
 
-        self.echo(DASHES)
-        self.echo("From the packages below:")
+        self.echo(DASHES, lineno=401)
+        self.echo("From the packages below:", lineno=402)
         self.local("packageLocation", "1")            # setup.sh:404-405
         self.local("countPackages")
         count, package_at = self._print_menu(packages, "k4-highcpu-kvm-7.75G=", "package")
@@ -658,7 +669,7 @@ class Supervisor:
                         self.echo(line)
                 if bad == 0:
                     v["HOST_PACKAGE"] = self.package_id(self.args_of(answer))
-                    self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]))
+                    self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]), lineno=440)
                     return
             elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"])):
                 v["gotValidInput"] = "true"
@@ -715,22 +726,22 @@ class Supervisor:
     # ------------------------------------------------------------------
     def verify_config(self) -> None:
         v = self.v
-        self.echo(RULE)
-        self.echo("Verify that the following configuration is correct:")
-        self.echo("")
-        self.echo("Name of kubernetes environment: %s" % v["KUBERNETES_NAME"])
-        self.echo("Kubernetes environment description: %s" % v["KUBERNETES_DESCRIPTION"])
-        self.echo("Master hostname: %s" % v["RANCHER_MASTER_HOSTNAME"])
-        self.echo("All node hostnames will start with: %s" % v["KUBERNETES_NODE_HOSTNAME_BEGINSWITH"])
-        self.echo("Kubernetes environment will have %s nodes" % v["KUBERNETES_NUMBER_OF_NODES"])
-        self.echo("Master server will be part of these networks: %s" % v["RANCHER_MASTER_NETWORKS"])
-        self.echo("Kubernetes nodes will be a part of these networks: %s" % v["KUBERNETES_NODE_NETWORKS"])
-        self.echo("This package will be used for all the hosts: %s" % v["HOST_PACKAGE"])
-        self.echo("")
-        self.echo("Make sure the above information is correct before answering:")
-        self.echo('    to view list of networks call "triton networks -l"')
-        self.echo('    to view list of packages call "triton packages -l"')
-        self.echo("WARN: Make sure that the nodes and master are part of networks that can communicate with each other and this system from which the setup is running.")
+        self.echo(RULE, lineno=453)
+        self.echo("Verify that the following configuration is correct:", lineno=454)
+        self.echo("", lineno=455)
+        self.echo("Name of kubernetes environment: %s" % v["KUBERNETES_NAME"], lineno=456)
+        self.echo("Kubernetes environment description: %s" % v["KUBERNETES_DESCRIPTION"], lineno=457)
+        self.echo("Master hostname: %s" % v["RANCHER_MASTER_HOSTNAME"], lineno=458)
+        self.echo("All node hostnames will start with: %s" % v["KUBERNETES_NODE_HOSTNAME_BEGINSWITH"], lineno=459)
+        self.echo("Kubernetes environment will have %s nodes" % v["KUBERNETES_NUMBER_OF_NODES"], lineno=460)
+        self.echo("Master server will be part of these networks: %s" % v["RANCHER_MASTER_NETWORKS"], lineno=461)
+        self.echo("Kubernetes nodes will be a part of these networks: %s" % v["KUBERNETES_NODE_NETWORKS"], lineno=462)
+        self.echo("This package will be used for all the hosts: %s" % v["HOST_PACKAGE"], lineno=463)
+        self.echo("", lineno=464)
+        self.echo("Make sure the above information is correct before answering:", lineno=465)
+        self.echo('    to view list of networks call "triton networks -l"', lineno=466)
+        self.echo('    to view list of packages call "triton packages -l"', lineno=467)
+        self.echo("WARN: Make sure that the nodes and master are part of networks that can communicate with each other and this system from which the setup is running.", lineno=468)
         while True:
             yn, ok = self.rt.read("Is the above config correct (yes | no)? ")
             v["yn"] = yn
@@ -740,7 +751,7 @@ class Supervisor:
                 return
             if yn == "no":
                 raise ScriptExit(0)  # ./config stays behind
-            self.echo("Please answer yes or no.")
+            self.echo("Please answer yes or no.", lineno=480)
 
     # ------------------------------------------------------------------
     # a8  setConfigToFile  (setup.sh:199-208)
@@ -812,12 +823,12 @@ class Supervisor:
         v, rt = self.v, self.rt
         if rt.exists("terraform/rancher.tf"):
             # unreachable from main (guarded earlier) but part of the function
-            self.echo("warning: a previous terraform configuration has been found")
-            self.echo("    skipping terraform configuration and execution...")
+            self.echo("warning: a previous terraform configuration has been found", lineno=141)
+            self.echo("    skipping terraform configuration and execution...", lineno=142)
             return
-        self.echo("Generating terraform configs for environment...")
+        self.echo("Generating terraform configs for environment...", lineno=144)
         self.update_terraform_config(["provider", "triton"])
-        self.echo("    Master hostname: %s" % v.get("RANCHER_MASTER_HOSTNAME", ""))  # quotes and all (setup.sh:146)
+        self.echo("    Master hostname: %s" % v.get("RANCHER_MASTER_HOSTNAME", ""))  # quotes and all (setup.sh:146, lineno=146)
         self.update_terraform_config(["master"] + self.args_of(self.unq(v.get("RANCHER_MASTER_HOSTNAME", ""))))
         # for (( i = 1; i <= $KUBERNETES_NUMBER_OF_NODES; i++ )): the count is text
         # from ./config spliced into the test expression, `i` a global of the script
@@ -829,14 +840,14 @@ class Supervisor:
 
             i = v.get("i", "")
             prefix = v.get("KUBERNETES_NODE_HOSTNAME_BEGINSWITH", "")
-            self.echo("    Kubernetes node %s: %s%s" % (i, self.unq(prefix), i))
+            self.echo("    Kubernetes node %s: %s%s" % (i, self.unq(prefix), i), lineno=150)
             self.update_terraform_config(["host"] + self.args_of(self.unq("%s%s" % (prefix, i))))
             self.arith_eval("i++", 148, "((")
         self.cd("terraform")
-        self.echo("Starting terraform tasks")
+        self.echo("Starting terraform tasks", lineno=155)
         self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156))[0])
         self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157))[0])
-        self.echo("    terraform tasks completed")
+        self.echo("    terraform tasks completed", lineno=158)
         self.cd("..")
 
     def update_terraform_config(self, args: List[str]) -> None:
@@ -881,7 +892,7 @@ class Supervisor:
             for k, line in enumerate(block[1:]):
                 self.append_line(rel, line, 189 + k)
             return
-        self.echo("error: problem updating terraform configuration...")
+        self.echo("error: problem updating terraform configuration...", lineno=196)
         raise ScriptExit(1)
 
     # ------------------------------------------------------------------
@@ -890,9 +901,9 @@ class Supervisor:
     def create_ansible_configs(self) -> None:
         rt, v = self.rt, self.v
         if not rt.exists("terraform/masters.ip") or not rt.exists("terraform/hosts.ip"):
-            self.echo("Terraform had too many errors. Make sure you haven't reached your provisioning limit.")
+            self.echo("Terraform had too many errors. Make sure you haven't reached your provisioning limit.", lineno=118)
             raise ScriptExit(1)
-        self.echo("Creating ansible hosts file and variable files")
+        self.echo("Creating ansible hosts file and variable files", lineno=121)
         hosts = "ansible/hosts"
         if os.path.isdir(rt.path(hosts)) and not os.path.islink(rt.path(hosts)):
             raise ScriptExit(1)  # `rm -f` cannot remove a directory (message hidden by 2>/dev/null), errexit
@@ -902,7 +913,7 @@ class Supervisor:
         self._cat_append("terraform/masters.ip", hosts, 124)
         self.append_line(hosts, "[HOST]", 125)
         self._cat_append("terraform/hosts.ip", hosts, 126)
-        self.echo("    created: ansible/hosts")
+        self.echo("    created: ansible/hosts", lineno=127)
 
         vars_yml = "ansible/roles/ranchermaster/vars/vars.yml"
         try:
@@ -922,7 +933,7 @@ class Supervisor:
         self._rewrite_private_key_file("ansible/ansible.cfg", "ansible/tmp.cfg", ";", self.unq(v.get("SDC_KEY", "")),
                                        shown_src="ansible.cfg")
         self.cd("..")
-        self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml")
+        self.echo("    created: ansible/roles/ranchermaster/vars/vars.yml", lineno=136)
 
     def _cat_append(self, src: str, dst: str, lineno: int) -> None:
         """``cat src >> dst`` under errexit."""
@@ -1029,7 +1040,7 @@ class Supervisor:
         v["KUBERNETES_DASHBOARD_UP"], v["DASHBOARD_CONTAINER_COUNT"] = "false", "0"
         up = False
         while not up:
-            rt.out(".")
+            self.write_out(".", 62)
             self.must(rt.sleep(1, self.at(63)))
             # if ! ((`date +%s` % 15)): the clock reading is spliced into an arithmetic
             # expression.  Zero -- or an expression bash cannot evaluate -- means "poll now".
@@ -1066,25 +1077,22 @@ class Supervisor:
                     status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,
                                         "docker stop -t0 %s" % container], stdout=DEVNULL, stderr=DEVNULL)
                     self.must(status)
-                rt.out(".")
+                self.write_out(".", 80)
 
     # ------------------------------------------------------------------
     # cleanRunner  (setup.sh:484-521)
     # ------------------------------------------------------------------
     def clean_runner(self) -> None:
         rt = self.rt
-        self.echo("Clearing settings....")
+        self.echo("Clearing settings....", lineno=485)
         while True:
             if rt.exists("terraform/masters.ip"):
-                self.echo("WARNING: You are about to destroy the following KVMs associated with Rancher cluster:")
-                try:
-                    rt.out(rt.read_text("terraform/masters.ip"))
-                except OSError:
-                    raise ScriptExit(1)
-                try:
-                    rt.out(rt.read_text("terraform/hosts.ip"))
-                except OSError:
-                    raise ScriptExit(1)  # `cat … 2>/dev/null` still fails, errexit
+                self.echo("WARNING: You are about to destroy the following KVMs associated with Rancher cluster:", lineno=488)
+                for rel in ("terraform/masters.ip", "terraform/hosts.ip"):
+                    try:
+                        rt.out(rt.read_text(rel))
+                    except OSError:
+                        raise ScriptExit(1)  # `cat … 2>/dev/null` still fails (unreadable, or stdout gone): errexit
                 yn, ok = rt.read("Do you wish to destroy the KVMs and reset configuration (yes | no)? ")
             else:
                 yn, ok = rt.read("Do you wish to reset configuration (yes | no)? ")
@@ -1093,17 +1101,17 @@ class Supervisor:
                 raise ScriptExit(1)
             if yn == "yes":
                 self._clean()
-                self.echo("    All clear!")
+                self.echo("    All clear!", lineno=515)
                 return
             if yn == "no":
                 raise ScriptExit(0)
-            self.echo("Please answer yes or no.")
+            self.echo("Please answer yes or no.", lineno=518)
 
     def _clean(self) -> None:
         rt = self.rt
         if rt.exists("terraform/rancher.tf"):
             self.cd("terraform")
-            self.echo("    destroying images...")
+            self.echo("    destroying images...", lineno=500)
             rt.run(["terraform", "destroy", "-force"], cwd="terraform", stderr=DEVNULL)  # `|| true`
             self.cd("..")
         if (rt.exists("terraform/hosts.ip") and rt.exists("terraform/masters.ip")
@@ -1132,7 +1140,10 @@ class Supervisor:
         for rel in ["ansible/hosts"] + sh.glob_word("ansible/*retry", rt.root) + ["ansible/ansible.cfg.tmp"]:
             p = rt.path(rel)
             if os.path.isdir(p) and not os.path.islink(p):
-                rt.out("rm: cannot remove '%s': Is a directory\n" % rel)
+                try:
+                    rt.out("rm: cannot remove '%s': Is a directory\n" % rel)
+                except OSError:
+                    pass
                 failed = True
             elif os.path.lexists(p):
                 os.remove(p)
