@@ -130,10 +130,11 @@ class Supervisor:
             self.v.pop("OLDPWD", None)
 
     # ------------------------------------------------------------------
-    # `local`: a function's local variable shadows a global of the same name --
-    # including an exported one, which the function's children then do not see --
-    # until the function returns.  A `$(...)` subshell is the same thing seen from
-    # outside: what it assigns is gone afterwards.
+    # `local`: a function's local variable shadows a global of the same name until
+    # the function returns, and takes over its export attribute -- so when the
+    # operator's shell exports `tmp`, the function's children see the *local* tmp.
+    # A `$(...)` subshell is the same thing seen from outside: what it assigns is
+    # gone afterwards.
     # ------------------------------------------------------------------
     @contextlib.contextmanager
     def scope(self):
