@@ -346,6 +346,12 @@ EDGE += [
              triton_env=triton_env_text() + "export i network\nexport master yn\nunset yn\n",
              note="`export NAME` before NAME has a value: it is exported the moment the script assigns it (the loop "
                   "counter i reaches terraform as i=3); unset takes the attribute away again"),
+    Scenario(name="triton_env_unsets_pwd", stdin=BLANK8 + YES, triton_env=triton_env_text() + "unset PWD OLDPWD\n",
+             note="unset takes the export attribute with it: `cd` goes on working (from bash's own idea of the directory) and "
+                  "sets both variables again, but terraform and ansible no longer find them in their environment"),
+    Scenario(name="triton_env_unsets_pwd_only", stdin=BLANK8 + YES, triton_env=triton_env_text() + "unset PWD\n",
+             note="... while OLDPWD keeps its attribute: absent after the first cd (it was given the value of an unset PWD), "
+                  "exported again from the second cd on; PWD stays unexported"),
     # --- children that read the stdin they inherit ------------------------------------
     Scenario(name="stdin_taken_by_ssh_keygen", stdin="eaten by ssh-keygen\n" + BLANK8 + YES, stdin_eaters={"ssh-keygen--E": 1},
              note="stdin is read a byte at a time, so a child sees exactly what is left: here the first line"),

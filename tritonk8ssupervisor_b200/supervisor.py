@@ -124,10 +124,14 @@ class Supervisor:
             inherited_ok = pwd.startswith("/") and os.path.samefile(pwd, root)
         except OSError:
             inherited_ok = False
-        self.export("PWD", pwd if inherited_ok else os.path.realpath(root))
-        if "OLDPWD" in env and not os.path.isdir(env["OLDPWD"]):
-            del env["OLDPWD"]
+        #: bash's own idea of the working directory; `cd` works from it, not from $PWD (which `triton env` may unset)
+        self._cwd = pwd if inherited_ok else os.path.realpath(root)
+        self.export("PWD", self._cwd)
+        if "OLDPWD" not in env or not os.path.isdir(env["OLDPWD"]):
+            # no usable OLDPWD: the variable exists with the export attribute and no value until the first cd
+            env.pop("OLDPWD", None)
             self.v.pop("OLDPWD", None)
+            self.v.export_when_set.add("OLDPWD")
 
     # ------------------------------------------------------------------
     # `local`: a function's local variable shadows a global of the same name until
@@ -189,9 +193,20 @@ class Supervisor:
     def cd(self, rel: str) -> None:
         """``cd rel``: no process of ours changes directory (children are started
         with ``cwd=``), but PWD and OLDPWD are part of what they inherit."""
-        old = self.v.get("PWD", "")
-        self.export("OLDPWD", old)
-        self.export("PWD", os.path.normpath(os.path.join(old, rel)))
+        # plain assignments: both are exported because bash gave them the attribute at
+        # start-up, and stop being so once `triton env` has unset them
+        if "PWD" in self.v:
+            self.v["OLDPWD"] = self.v["PWD"]
+        else:
+            # OLDPWD=<value of an unset PWD>: no value for the shell; bash patches its cached
+            # environment in place, so children of the next commands find an empty OLDPWD
+            exported = "OLDPWD" in self.rt.env or "OLDPWD" in self.v.export_when_set
+            self.v.pop("OLDPWD", None)
+            if exported:
+                self.v.export_when_set.discard("OLDPWD")
+                self.rt.env["OLDPWD"] = ""
+        self._cwd = os.path.normpath(os.path.join(self._cwd, rel))
+        self.v["PWD"] = self._cwd
 
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
@@ -288,8 +303,6 @@ class Supervisor:
             return "0"
         if name == "FUNCNAME":
             return "main"
-        if name == "PWD":
-            return os.path.abspath(self.rt.root)
         return None
 
     def arith_eval(self, expr: str, lineno: int, command: str, last_status: int = 0) -> Optional[int]:
