@@ -96,6 +96,14 @@ class ModelRuntime(Runtime):
         self.calls.append("%s|%s|%s" % (tool, rel, " ".join(args)))
         # what stubtool.sh records of its environment: `env | grep -v | sort | sed`, line by line
         env = child_env(self.env, "%s/bin/%s" % (self._sbx, tool), lone_subst)
+        # the stub is a /bin/sh script, and dash exports a PWD of its own when it inherits none (or a wrong one)
+        here = os.path.normpath(os.path.join(self.root, cwd))
+        try:
+            inherited_ok = env.get("PWD", "").startswith("/") and os.path.samefile(env["PWD"], here)
+        except OSError:
+            inherited_ok = False
+        if not inherited_ok:
+            env["PWD"] = os.path.realpath(here)
         dump = "".join("%s=%s\n" % kv for kv in env.items())
         lines = sorted((l for l in dump.split("\n")[:-1] if not _ENV_HIDDEN.match(l)), key=bashsem.c_sort_key)
         lines = [l.replace(self._sbx, "<SBX>") for l in lines]
