@@ -94,3 +94,107 @@ def test_property_fuzzed_scenarios(ref_root, block):
         if diffs:
             bad.append((seed, sc.to_json(), diffs))
     assert bad == []
+
+
+# --- a wider variant: what the tools below the offline line print and leave behind ---------
+_PS = ["1111 img k8s_kubernetes-dashboard.a\n3333 pause k8s_POD.x_kubernetes-dashboard-1\n", "5555 agent rancher-agent\n", "",
+       "a b kubernetes-dashboard\nc d kubernetes-dashboard\n", "* k8s_POD.dashboard kubernetes-dashboard\n? x kubernetes-dashboard\n"]
+
+
+def make_wide(seed: int) -> Scenario:
+    import dataclasses
+    sc = make(seed)
+    r = random.Random(seed * 7 + 1)
+    kw = {}
+    if r.random() < 0.4:
+        kw["master_ip"] = r.choice(["10.0.0.1", "1.2.3.4 5.6.7.8", "*", "a b", "", "-n", "ter*"])
+    if r.random() < 0.4:
+        kw["env_id"] = r.choice(["1a7", "", "x y", "*", "1a7\n1a8", "-e"])
+    if r.random() < 0.5:
+        kw["ssh_ps"] = {"10.0.1.%d" % i: r.choice(_PS) for i in range(1, 4)}
+        kw["curl_seq"] = [r.choice(["starting\n", "", "503 Service Unavailable\n", "service unavailable", "KuBeRnEtEs", "* ?\n"])
+                          for _ in range(r.randint(0, 4))]
+    if r.random() < 0.3:
+        kw["known_hosts"] = "x\n"
+    if r.random() < 0.3:
+        kw["keygen_no_E"] = True
+    if r.random() < 0.3:
+        kw["keygen"] = {"id_rsa": r.choice(["2048 MD5:aa:bb:cc:dd c (RSA)\n", "2048 MD5:zz c\n", "", "one\n", "a b c\nd e f\n", "2048 * c\n"])}
+        kw["keygen_sha"] = {"id_rsa": r.choice(["2048 SHA256:zz c\n", "2048 aa:bb:cc:dd c\n", "", "x SHA256\n"])}
+    if r.random() < 0.3 and not sc.stdin.startswith("yes"):
+        kw["stdin"] = "\n" * 4 + r.choice(["", "1", "2", "3", "9"]) + "\n\n\n\nyes\n" + sc.stdin
+    if r.random() < 0.2:
+        kw["terraform_no_ips"] = True
+    if r.random() < 0.15:
+        kw["invocation"] = "bash setup.sh"
+    if r.random() < 0.1:
+        kw["home_name"] = r.choice(["my home", "h*me", "h[o]me"])
+    if r.random() < 0.1:
+        kw["unset_env"] = [r.choice(["LC_ALL", "SHLVL"])]
+    return dataclasses.replace(sc, **kw)
+
+
+# --- and one for the state of the workspace: files, directories and links in the way ------------
+_PATHS = ["config", "config.tmp", "tmp", "terraform/rancher.tf", "terraform/masters.ip", "terraform/hosts.ip", "terraform/terraform.tfstate",
+          "terraform/.terraform", "ansible/hosts", "ansible/ansible.cfg", "ansible/tmp.cfg", "ansible/ansible.cfg.tmp", "ansible/a.retry",
+          "ansible/roles/ranchermaster/vars/vars.yml", "ansible/tmp/kubernetes_environment.id", "ansible/tmp", "tmp/x"]
+#: link targets stay inside the sandbox or point nowhere: the reference's `rm -rf tmp/*` goes *through* a link to a
+#: directory, and a target such as /tmp would have it empty that directory for real
+_TARGETS = ["/dev/null", "nowhere", "../config", "clusterUp.yml", "../ansible/ansible.cfg", "hosts", "/nonexistent/x", "ansible",
+            "../terraform", "roles", "ansible.cfg"]
+_CFGS = ["[defaults]\nprivate_key_file = old\n", "private_key_file = a\nprivate_key_file = b", "", "x\n",
+         "[defaults]\r\nprivate_key_file = q\r\n", "# private_key_file = c\n private_key_file = d\n"]
+
+
+def make_workspace(seed: int) -> Scenario:
+    r = random.Random(seed)
+    kw = dict(name="ws%d" % seed, args=["-c"] if r.random() < 0.4 else [],
+              stdin=r.choice(["yes\n", "no\n", "yes\nyes\n", "\n" * 8 + "yes\n", "yes\n" + "\n" * 8 + "yes\n", "\n\n\n\n2\n\n\n\nyes\nyes\n"]))
+    pre_files, pre_remove, pre_symlinks = {}, [], {}
+    for _ in range(r.randint(0, 4)):
+        p, k = r.choice(_PATHS), r.random()
+        if k < 0.35:
+            pre_files[p] = r.choice(_CFGS) if p.endswith("cfg") else r.choice(["x\n", "", "10.9.9.9\n", "a b\n*\n", "1a9"])
+        elif k < 0.5:
+            pre_files[p + "/keep"] = "k\n"
+        elif k < 0.7:
+            pre_remove.append(p)
+        else:
+            pre_symlinks[p] = r.choice(_TARGETS)
+    taken = pre_remove + list(pre_symlinks)
+    pre_files = {p: c for p, c in pre_files.items() if not any(p == q or p.startswith(q + "/") or q.startswith(p + "/") for q in taken)}
+    pre_files = {p: c for p, c in pre_files.items() if not any(q != p and q.startswith(p + "/") for q in pre_files)}
+    pre_symlinks = {p: t for p, t in pre_symlinks.items() if not any(p != q and p.startswith(q + "/") for q in taken)}
+    kw.update(pre_files=pre_files, pre_remove=pre_remove, pre_symlinks=pre_symlinks)
+    if r.random() < 0.3:
+        kw["known_hosts"] = "h\n"
+    if r.random() < 0.2:
+        kw["env_id"] = "1b2"
+    if r.random() < 0.15:
+        kw["fail"] = {r.choice(["terraform-destroy", "terraform-apply", "ssh-keygen--R", "ansible-playbook--i"]): 1}
+    return Scenario(**kw)
+
+
+def _sweep(ref_root, generator, seeds):
+    bad = []
+    for seed in seeds:
+        try:
+            sc = generator(seed)
+            theirs = run_reference(sc, ref_root)
+            mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+        except OSError:
+            continue        # the generator asked for a workspace that cannot be laid down (a file inside a link ...)
+        diffs = theirs.diff(mine)
+        if diffs:
+            bad.append((seed, sc.to_json(), diffs))
+    return bad
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_tools(ref_root, block):
+    assert _sweep(ref_root, make_wide, range(20000 + 15 * block, 20000 + 15 * (block + 1))) == []
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_workspaces(ref_root, block):
+    assert _sweep(ref_root, make_workspace, range(30000 + 25 * block, 30000 + 25 * (block + 1))) == []
