@@ -461,4 +461,12 @@ TTY_CASES = [
     (Scenario(name="tty_clean", args=["-c"], pre_files={"terraform/masters.ip": "10.0.0.1\n", "terraform/hosts.ip": "10.0.1.1\n"},
               note="clean prompt wording when machines exist (setup.sh:487-493)"), ["what", "yes"]),
     (Scenario(name="tty_clean_fresh", args=["-c"], note="clean prompt wording on a fresh tree (setup.sh:495)"), ["no"]),
+    (Scenario(name="tty_key_not_found", keygen={"id_rsa": "2048 MD5:ff:ff:ff:ff other (RSA)\n"},
+              note="no key matches the profile: the three error lines, then the clean prompt"), ["maybe", "yes"]),
+    (Scenario(name="tty_stale_config", pre_files={"config": "OLD=1\n"},
+              note="an old ./config: clean is offered first, then the ordinary prompts follow"),
+     ["yes", "", "", "", "", "", "", "", "", "no"]),
+    (Scenario(name="tty_clock_is_not_a_number", date_seq=["08", "15 30"], curl_seq=["<html>starting</html>\n"],
+              note="bash's arithmetic diagnostics land on the terminal between the progress dots"),
+     ["", "", "", "", "", "", "", "", "yes"]),
 ]
