@@ -22,6 +22,8 @@ import os
 import re
 from typing import Callable, List, Optional, Sequence, Tuple
 
+from . import shmatch
+
 IFS_WS = " \t\n"
 
 
@@ -147,119 +149,21 @@ def _has_glob_chars(word: str) -> bool:
     return False
 
 
-_CLASSES = {
-    "alpha": "a-zA-Z", "digit": "0-9", "alnum": "0-9a-zA-Z", "upper": "A-Z", "lower": "a-z",
-    "space": " \\t\\n\\r\\f\\v", "blank": " \\t", "punct": re.escape("!\"#$%&'()*+,-./:;<=>?@[\\]^_`{|}~"),
-    "print": "\\x20-\\x7e", "graph": "\\x21-\\x7e", "cntrl": "\\x00-\\x1f\\x7f", "xdigit": "0-9A-Fa-f",
-    "word": "0-9a-zA-Z_",
-}
-
-
-def _bracket_to_regex(pat: str, i: int) -> Tuple[Optional[str], int]:
-    """Translate the bracket expression starting after '[' at pat[i:].
-    Returns (regex, index after ']') or (None, i) when there is no closing ']'
-    (the '[' is then an ordinary character)."""
-    n = len(pat)
-    j = i
-    negate = False
-    if j < n and pat[j] in "!^":
-        negate = True
-        j += 1
-    items: List[str] = []
-    first = True
-    while True:
-        if j >= n:
-            return None, i
-        c = pat[j]
-        if c == "]" and not first:
-            j += 1
-            break
-        first = False
-        if c == "[" and j + 1 < n and pat[j + 1] in ":.=":
-            kind = pat[j + 1]
-            close = pat.find(kind + "]", j + 2)
-            if close != -1:
-                name = pat[j + 2:close]
-                if kind == ":":
-                    if name not in _CLASSES:
-                        return None, i
-                    items.append(_CLASSES[name])
-                else:
-                    items.append(re.escape(name))
-                j = close + 2
-                continue
-        if c == "\\" and j + 1 < n:
-            j += 1
-            c = pat[j]
-        if c == "/":
-            # a slash cannot be matched by a bracket expression in a pathname
-            return None, i
-        lo = c
-        j += 1
-        if j + 1 < n and pat[j] == "-" and pat[j + 1] != "]":
-            hi = pat[j + 1]
-            j += 2
-            if hi == "\\" and j < n:
-                hi = pat[j]
-                j += 1
-            if ord(lo) > ord(hi):
-                # invalid range: matches nothing (bash returns no match)
-                items.append("")
-                continue
-            items.append("%s-%s" % (re.escape(lo), re.escape(hi)))
-        else:
-            items.append(re.escape(lo))
-    body = "".join(items)
-    if not body:
-        return ("[\\s\\S]" if negate else "(?!)"), j
-    return "[%s%s]" % ("^" if negate else "", body), j
-
-
-def glob_to_regex(pat: str, pathname: bool = True) -> str:
-    """Shell pattern -> anchored Python regex (C locale)."""
-    out: List[str] = []
-    i, n = 0, len(pat)
-    nonslash = "[^/]" if pathname else "[\\s\\S]"
-    while i < n:
-        c = pat[i]
-        i += 1
-        if c == "*":
-            out.append(nonslash + "*")
-        elif c == "?":
-            out.append(nonslash)
-        elif c == "[":
-            rx, j = _bracket_to_regex(pat, i)
-            if rx is None:
-                out.append(re.escape("["))
-            else:
-                out.append(rx)
-                i = j
-        elif c == "\\":
-            if i < n:
-                out.append(re.escape(pat[i]))
-                i += 1
-            else:
-                out.append(re.escape("\\"))
-        else:
-            out.append(re.escape(_unquote(c)))
-    return "(?s:" + "".join(out) + r")\Z"
-
-
 def pattern_match(s: str, pat: str) -> bool:
-    """``[[ $s == $pat ]]`` with an unquoted right-hand side (setup.sh:345,388,442)."""
-    return re.match(glob_to_regex(pat, pathname=False), s) is not None
+    """``[[ $s == $pat ]]`` with an unquoted right-hand side (setup.sh:351,394,443):
+    a pattern match, with the extended operators bash switches on inside ``[[ ]]``."""
+    return shmatch.strmatch(pat, s, shmatch.EXTMATCH)
 
 
 def _glob_component(pattern: str) -> Callable[[str], bool]:
-    rx = re.compile(glob_to_regex(pattern, pathname=True))
-    leading_dot_ok = pattern.startswith(".") or pattern.startswith("\\.")
+    """Matcher for one pathname component (no extended operators: extglob is off in a script)."""
+    # quoted text (see quote_for_glob) reaches the matcher as backslash-escaped characters
+    pattern = "".join("\\" + _unquote(c) if _unquote(c) != c else c for c in pattern)
 
     def match(name: str) -> bool:
         if name in (".", ".."):
             return False  # globskipdots (default on in bash 5.2)
-        if name.startswith(".") and not leading_dot_ok:
-            return False
-        return rx.match(name) is not None
+        return shmatch.strmatch(pattern, name, shmatch.PERIOD)
     return match
 
 

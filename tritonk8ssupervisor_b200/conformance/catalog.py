@@ -107,6 +107,15 @@ EDGE: List[Scenario] = [
              packages=triton_table([("k4-highcpu-kvm-7.75G", "q*q")]),
              stdin=_answers("", "", "", "", "", "zqz-9", "nomatch", "", "qxyzq", "yes"),
              note="[[ $answer == $default ]] has an unquoted right-hand side: the default is a *pattern* (setup.sh:345,388,442)"),
+    Scenario(name="net_default_with_extended_pattern", networks=triton_table([("Joyent-SDC-Public", "@(abc|x?z)+(-)!(q)")]),
+             stdin=_answers("", "", "", "", "", "xyz-r", "abd-", "abc--", "", "yes"),
+             note="inside [[ ]] the pattern operators ?() *() +() @() !() are on: a default of '@(abc|x?z)+(-)!(q)' accepts "
+                  "'xyz-r' and 'abc--', not 'abd-'"),
+    Scenario(name="pkg_default_is_a_broken_pattern",
+             packages=triton_table([("k4-highcpu-kvm-7.75G", "[a-"), ("k4-highcpu-kvm-1.75G", "14b5edc4-d0f8-11e5-b4d2-b3e6e8c05f9d")]),
+             stdin=_answers("", "", "", "", "", "", "", "", "[a-", "1", "yes"),
+             note="a '[' that finds no ']' is an ordinary character -- unless the search runs into a dangling range: '[a-' "
+                  "matches nothing, not even itself, so the empty answer (= the default) is rejected until an index is typed"),
     Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
              stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
     Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),
