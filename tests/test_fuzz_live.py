@@ -198,3 +198,50 @@ def test_property_fuzzed_tools(ref_root, block):
 @pytest.mark.parametrize("block", range(3))
 def test_property_fuzzed_workspaces(ref_root, block):
     assert _sweep(ref_root, make_workspace, range(30000 + 25 * block, 30000 + 25 * (block + 1))) == []
+
+
+# --- and one for the shape of what `triton networks|packages` prints ---------------------------
+_TCH = list("abK-=_ .*?[]\t\r0123()|@+!^:") + ["-kvm-", "  ", "NAME", "ID", "Joyent-SDC-Public", "k4-highcpu-kvm-7.75G", "é", "\\"]
+
+
+def _odd_table(r):
+    def word(k=4):
+        return "".join(r.choice(_TCH) for _ in range(r.randint(1, k)))
+    lines = [r.choice(["NAME  ID", "NAME ID", "NAME    ID  ", "name id", "", "NAMEID", "NAME\tID"])]
+    for _ in range(r.randint(0, 7)):
+        shape = r.choice(["{}  {}", "{} {}", "{}\t{}", "{}", " {}  {} ", "{}  {}  extra"])
+        lines.append(shape.format(word(), word())[:60])
+    if r.random() < 0.2:
+        lines.insert(r.randint(0, len(lines)), "")
+    return "\n".join(lines) + r.choice(["\n", "", "\n\n"])
+
+
+def make_tables(seed: int) -> Scenario:
+    r = random.Random(seed)
+    answers = ["", "", "", "", r.choice(["", "2"]), r.choice(["", "1", "2,1", "3", "1,2,3"]), r.choice(["", "1", "2"]),
+               r.choice(["", "1", "2", "3"]), "", "", "", "yes", "yes"]
+    return Scenario(name="tb%d" % seed, stdin="".join(a + "\n" for a in answers), networks=_odd_table(r), packages=_odd_table(r))
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_tables(ref_root, block):
+    """A default that is a pattern matching nothing (an id such as ``[a-``) makes the
+    reference re-prompt for ever once stdin is exhausted; then both must spin."""
+    import subprocess
+    from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox
+    bad = []
+    for seed in range(3000 + 12 * block, 3000 + 12 * (block + 1)):
+        sc = make_tables(seed)
+        res = []
+        for argv, env in ((sc.reference_argv(), None), (rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV)):
+            with Sandbox(ref_root, sc) as sbx:
+                try:
+                    res.append(sbx.run(argv, env, timeout=10))
+                except subprocess.TimeoutExpired:
+                    res.append(None)
+        if res[0] is None or res[1] is None:
+            if (res[0] is None) != (res[1] is None):
+                bad.append((seed, "only one of the two never ends", sc.to_json()))
+        elif res[0].diff(res[1]):
+            bad.append((seed, res[0].diff(res[1]), sc.to_json()))
+    assert bad == []
