@@ -74,7 +74,7 @@ def test_same_variables_as_bash_eval(text):
     'export SDC_URL="$((1+1))"\n', 'export SDC_URL="${HOME:-x}"\n', 'export SDC_URL="${HOME"\n', "export SDC_URL=$1\n",
     'export SDC_URL="$?"\n', "export SDC_URL=$'ansi'\n", "unset $HOME\n", "$HOME\n", "export $HOME=x\n", "export SDC_URL=$_\n",
     "export SDC_URL=~+/x\n", "export SDC_URL=${!HOME}\n", "export SDC_URL=$$\n",
-    "export IFS=:\n", "IFS=,\n", "unset IFS\n", "export LC_ALL=en_US.UTF-8\n", "GLOBIGNORE=*\n",
+    "export\n", "export IFS=:\n", "IFS=,\n", "unset IFS\n", "export LC_ALL=en_US.UTF-8\n", "GLOBIGNORE=*\n",
 ])
 def test_everything_else_is_refused(text):
     with pytest.raises(TritonEnvError):
@@ -95,3 +95,56 @@ def test_refusal_end_to_end(tmp_path):
     assert not marker.exists()
     assert "terraform/rancher.tf" not in obs.files
     assert [c.split("|")[0] for c in obs.calls if not c.startswith("  env")] == ["triton"]
+
+
+# --- random texts of the accepted dialect: whatever is not refused must leave what bash's eval leaves ----
+_VAL = ["x", "y z", "$A", "${B}", "$PLAIN", "$HOME", "~", "~/", ":", "/p", "a=b", "é", "*", "?", "[", "~root", "-", "$", "\\ ", "#h",
+        "'q $A'", '"d $A ~"', '"\\$A"', "\\$A", "=", "+", "{a,b}", "$[1]"]
+
+
+def _random_text(r):
+    out = []
+    for _ in range(r.randint(1, 4)):
+        k = r.random()
+        name = r.choice(["A", "B", "SDC_URL", "PLAIN", "EMPTY"])
+        val = "".join(r.choice(_VAL) for _ in range(r.randint(0, 4)))
+        if k < 0.5:
+            out.append("export %s=%s" % (name, val))
+        elif k < 0.7:
+            out.append("%s=%s" % (name, val))
+        elif k < 0.8:
+            out.append("unset %s" % name)
+        elif k < 0.9:
+            out.append("export %s %s=%s" % (name, r.choice(["A", "B"]), val))
+        else:
+            out.append("# " + val)
+        out.append(r.choice(["\n", ";", " ;\n", "\n\n", " # c\n"]))
+    return "".join(out)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_random_accepted_texts_match_bash_eval(seed):
+    import random
+    r = random.Random(seed)
+    accepted = 0
+    for _ in range(120):
+        text = _random_text(r)
+        try:
+            mine = ours(text)
+        except TritonEnvError:
+            continue
+        accepted += 1
+        assert mine == bash_eval(text), text
+    assert accepted > 40
+
+
+@pytest.mark.parametrize("text", ["export A={a,b}\n", "export A=x{1..3}\n", "export A=$[1+1]\n", "unset {A,B}\n"])
+def test_expansions_of_command_words_are_refused(text):
+    with pytest.raises(TritonEnvError):
+        apply_triton_env(text, {}, {})
+
+
+def test_plain_assignment_has_no_brace_expansion():
+    shell, env = {}, {}
+    apply_triton_env("A={a,b}\n", shell, env)
+    assert shell == {"A": "{a,b}"} and env == {}

@@ -59,7 +59,7 @@ def _parameter(text: str, i: int, quoted: bool) -> Tuple[Optional[_Var], int]:
     m = _NAME_AT.match(text, i + 1)
     if m and m.group(0) != "_":
         return _Var(m.group(0), quoted), m.end()
-    special = nxt != "" and (nxt in "(0123456789?$!#@*-_" or (nxt in "'\"" and not quoted))
+    special = nxt != "" and (nxt in "([0123456789?$!#@*-_" or (nxt in "'\"" and not quoted))
     if special:
         # $(...), positional and special parameters, $'...' and $"..."
         raise TritonEnvError("refusing to evaluate an expansion in `triton env` output: %r" % text[i:i + 20])
@@ -144,6 +144,10 @@ def _split_commands(text: str) -> List[List[List[_Piece]]]:
             have_word = True
         elif c in "`()<>|&":
             raise TritonEnvError("refusing to evaluate shell syntax in `triton env` output: %r" % text[i:i + 20])
+        elif c == "{" and words and not isinstance(words[0][0], _Var) and "".join(
+                p[0] for p in words[0] if not isinstance(p, _Var)) in ("export", "unset"):
+            # arguments of a command undergo brace expansion ({a,b}, {1..3}); a plain assignment does not
+            raise TritonEnvError("refusing to evaluate a brace expression in `triton env` output: %r" % text[i:i + 20])
         else:
             cur.append((c, False))
             have_word = True
@@ -232,9 +236,14 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
         return "".join(p[0] for p in word)        # type: ignore[index]
 
     pending = getattr(shell_vars, "export_when_set", None)
+    if pending is None:
+        pending = set()         # a plain dict: the attribute is remembered for the rest of this text at least
     for words in _split_commands(text):
         head = plain(words[0]) if not any(isinstance(p, _Var) for p in words[0]) else None
         if head == "export":
+            if len(words) == 1:
+                # a bare `export` lists every exported variable on the script's stdout
+                raise TritonEnvError("refusing to run a bare `export` from `triton env` output")
             for w in words[1:]:
                 parsed = _assignment(w, shell_vars, tilde_home)
                 if parsed is None:
@@ -245,7 +254,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                     shell_vars[name] = value
                 if name in shell_vars:
                     env[name] = shell_vars[name]
-                elif pending is not None:
+                else:
                     pending.add(name)           # `export NAME` before NAME has a value: exported once it gets one
         elif head == "unset":
             for w in words[1:]:
@@ -253,8 +262,7 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                 _guard(name)
                 shell_vars.pop(name, None)
                 env.pop(name, None)
-                if pending is not None:
-                    pending.discard(name)
+                pending.discard(name)
         else:
             parsed = _assignment(words[0], shell_vars, tilde_home) if len(words) == 1 else None
             if parsed is None or parsed[1] is None:
@@ -262,7 +270,8 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
             name, value = parsed
             _guard(name)
             shell_vars[name] = value
-            if name in env:
+            if name in env or name in pending:
+                pending.discard(name)
                 env[name] = value
 
 
