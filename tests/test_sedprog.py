@@ -38,10 +38,54 @@ def test_against_real_sed(tmp_path, value, text):
 
 def test_e_flag_is_refused_not_run():
     res = sedprog.run(CFG, "a;e", ";")
-    assert not res.ok and "unknown option" in res.error
+    assert not res.ok and "e flag" in res.refused and res.error == ""
+
+
+# no 'e'/'E' in the alphabet (the e flag, the e command), no '/' (files stay in the scratch directory)
+_CH = list("ab;&\\gpwiIdDhHxnNqP{}0123 #~!$=") + ["\\n", "\\&", ";;", "w o", "\\;", "2g", "gp", "pw x", "\\\\", "\n", "\\x41", "\\t"]
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_random_values_against_real_sed(tmp_path, seed):
+    """Whatever the module does not refuse, it must do exactly as sed does: output, files written, messages."""
+    import random
+    r = random.Random(seed)
+    checked = 0
+    for _ in range(150):
+        value = "".join(r.choice(_CH) for _ in range(r.randint(0, 6)))
+        text = r.choice([CFG, CFG[:-1], "", "private_key_file = only", "x\nprivate_key_file = q\n"])
+        res = sedprog.run(text, value, ";")
+        if res.refused:
+            continue
+        for f in os.listdir(str(tmp_path)):
+            os.remove(os.path.join(str(tmp_path), f))
+        rc, out, err = real_sed(value, text, tmp_path)
+        checked += 1
+        assert res.ok == (rc == 0), (value, err, res.error)
+        if rc == 0:
+            assert res.output == out, value
+            assert res.wfiles == {f: open(os.path.join(str(tmp_path), f)).read() for f in os.listdir(str(tmp_path))}, value
+        else:
+            assert res.error == err, value
+    assert checked > 60
 
 
 def test_clean_form():
     """setup.sh:511: delimiter ~ and an empty value."""
     res = sedprog.run(CFG, "", "~")
     assert res.ok and "private_key_file = \n" in res.output and "old" not in res.output
+
+
+def test_unrestated_program_is_refused_end_to_end():
+    """A key file called ``k;;=``: the reference's sed would go on with the ``=`` command (print
+    line numbers into ansible.cfg); the replacement stops with status 2 and says why."""
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE
+    from tritonk8ssupervisor_b200.conformance.sandbox import run_in_sandbox
+    from tritonk8ssupervisor_b200.conformance.scenario import DEFAULT_KEY_ID, Scenario
+    sc = Scenario(name="sedmore", stdin="\n" * 8 + "yes\n", ssh_files={"k;;=": "K\n"},
+                  keygen={"k;;=": "2048 MD5:%s c (RSA)\n" % DEFAULT_KEY_ID}, keygen_sha={})
+    obs = run_in_sandbox(rp.REPLACEMENT_ARGV, WORKSPACE_TEMPLATE, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert obs.exit_status == 2
+    assert "refusing to go on: the key path spliced into the sed program at line 133" in obs.stderr
+    assert "ansible/ansible.cfg" not in obs.files          # untouched

@@ -16,8 +16,11 @@ name, but it is what the reference does, so it is restated here (GNU sed 4.8
 rules, ``sed/compile.c:mark_subst_opts``; third-party, checked against the real
 ``sed`` in tests/test_sedprog.py).
 
-Not restated on purpose: the ``e`` flag (execute the pattern space as a shell
-command).  It is refused like a syntax error.
+Restated: the replacement syntax, every flag of ``s`` but one, and the commands
+``g G h H x p d q`` after it.  Refused (the caller stops with status 2) rather
+than guessed at: the ``e`` flag, which would execute the pattern space as a shell
+command, and a value that goes on with any other sed command, a block or an
+address -- all legal sed, all absurd in the name of a key file.
 """
 from __future__ import annotations
 
@@ -31,8 +34,43 @@ VALUE_AT = len("s;" + "private_key_file = .*$" + ";" + PREFIX) + 1
 
 
 class SedResult:
-    def __init__(self, ok: bool, output: str = "", error: str = "", wfiles: Optional[Dict[str, str]] = None):
+    def __init__(self, ok: bool, output: str = "", error: str = "", wfiles: Optional[Dict[str, str]] = None,
+                 refused: str = ""):
         self.ok, self.output, self.error, self.wfiles = ok, output, error, wfiles or {}
+        #: non-empty: the value continues the program with something sed would accept and this module
+        #: does not restate (or would not run: the e flag) -- the caller must stop, not guess
+        self.refused = refused
+
+
+def _refuse(what: str) -> SedResult:
+    return SedResult(False, refused=what)
+
+
+#: what may legitimately follow the s command in GNU sed and is not restated here: other commands,
+#: blocks, and anything that starts an address
+_NOT_RESTATED = set("abcDeFilLnNPQrRstTvwWyz=:{!$/\\0123456789~")
+_SIMPLE_ESCAPES = {"a": "\a", "f": "\f", "r": "\r", "t": "\t", "v": "\v"}
+
+
+def _gnu_escape(text: str, at: int) -> Optional[Tuple[str, int]]:
+    """GNU sed's character escapes in a replacement: ``\\a \\f \\r \\t \\v``, ``\\cX``, ``\\dNNN``,
+    ``\\oNNN``, ``\\xHH``.  ``text[at]`` is the character after the backslash; returns
+    (character, index after the escape) or None when it is not one of these."""
+    d = text[at]
+    if d in _SIMPLE_ESCAPES:
+        return _SIMPLE_ESCAPES[d], at + 1
+    if d == "c" and at + 1 < len(text):
+        return chr(ord(text[at + 1].upper()) ^ 0x40), at + 2
+    for letter, digits, base, width in (("d", "0123456789", 10, 3), ("o", "01234567", 8, 3), ("x", "0123456789abcdefABCDEF", 16, 2)):
+        if d == letter:
+            j = at + 1
+            while j < len(text) and j - at - 1 < width and text[j] in digits:
+                j += 1
+            if j == at + 1:
+                return None
+            return bytes([int(text[at + 1:j], base) & 0xFF]).decode("utf-8", "surrogateescape"), j
+    return None
+
 
 
 def _fail(pos: int, what: str) -> SedResult:
@@ -46,13 +84,25 @@ def run(text: str, value: str, delim: str) -> SedResult:
     parts: List[Tuple[str, str]] = []
     i, n = 0, len(program_tail)
     closed = False
+    bad_reference: Optional[SedResult] = None
     while i < n:
         c = program_tail[i]
         if c == "\\" and i + 1 < n:
             d = program_tail[i + 1]
             if d in "123456789":
-                # compile.c reports it once the whole command has been read
-                return _fail(VALUE_AT + _end_of_s(program_tail, i, delim), "invalid reference \\%s on `s' command's RHS" % d)
+                # compile.c reports it once the whole command has been read -- if it can be read
+                if bad_reference is None:
+                    bad_reference = _fail(VALUE_AT + _end_of_s(program_tail, i, delim),
+                                          "invalid reference \\%s on `s' command's RHS" % d)
+                i += 2
+                continue
+            if d in "LUluE":
+                return _refuse("a case conversion (\\%s) in the replacement" % d)
+            esc = _gnu_escape(program_tail, i + 1)
+            if esc is not None:
+                parts.append(("lit", esc[0]))
+                i = esc[1]
+                continue
             parts.append(("lit", "\n") if d == "n" else ("match", "") if d == "0" else ("lit", d))
             i += 2
             continue
@@ -61,11 +111,13 @@ def run(text: str, value: str, delim: str) -> SedResult:
             i += 1
             break
         if c == "\n":
-            return _fail(VALUE_AT + i, "unterminated `s' command")
+            return _fail(VALUE_AT + i - 1, "unterminated `s' command")
         parts.append(("match", "") if c == "&" else ("lit", c))
         i += 1
     if not closed:
         return _fail(VALUE_AT + n - 1, "unterminated `s' command")
+    if bad_reference is not None:
+        return bad_reference
 
     # --- flags of s -------------------------------------------------------------
     flag_g = flag_p = icase = False
@@ -98,13 +150,15 @@ def run(text: str, value: str, delim: str) -> SedResult:
             i = j
             continue
         elif c == "w":
-            wfile = program_tail[i + 1:].split("\n", 1)[0].lstrip(" \t")
+            rest = program_tail[i + 1:]
+            wfile = rest.split("\n", 1)[0].lstrip(" \t")
             if not wfile:
                 return _fail(VALUE_AT + n - 1, "missing filename in r/R/w/W commands")
-            i = n
+            # the file name runs to the end of the line; a newline in the value lets the program go on after it
+            i = i + 1 + rest.index("\n") if "\n" in rest else n
             break
         elif c == "e":
-            return _fail(pos, "unknown option to `s'")      # deliberately not supported (would run a shell command)
+            return _refuse("the e flag of sed's s command (it would run the pattern space as a shell command)")
         elif c in " \t":
             pass
         elif c in ";\n#}":
@@ -127,10 +181,23 @@ def run(text: str, value: str, delim: str) -> SedResult:
         elif c in "gpdhxGHq":
             commands.append(c)
             i += 1
+            if c == "q":                      # q takes an optional exit status
+                j = i
+                while j < n and program_tail[j] in " \t":
+                    j += 1
+                k = j
+                while k < n and program_tail[k].isdigit():
+                    k += 1
+                if k > j:
+                    if int(program_tail[j:k]) != 0:
+                        return _refuse("a q command with a non-zero exit status")
+                    i = k
             while i < n and program_tail[i] in " \t":
                 i += 1
             if i < n and program_tail[i] not in ";\n#}":
                 return _fail(VALUE_AT + i, "extra characters after command")
+        elif c in _NOT_RESTATED:
+            return _refuse("the sed program continues with %r, which is not restated here" % program_tail[i:i + 12])
         else:
             return _fail(VALUE_AT + i, "unknown command: `%s'" % c)
 
@@ -227,4 +294,6 @@ def _end_of_s(tail: str, start: int, delim: str) -> int:
     j = i + 1
     while j < n and tail[j] not in ";\n}#":
         j += 1
+    if j < n and tail[j] in ";\n":
+        return j                      # the separator has been read by then
     return min(j, n) - 1

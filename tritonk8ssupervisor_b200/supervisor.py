@@ -979,6 +979,10 @@ class Supervisor:
         except OSError as exc:
             text, readable, why = "", False, exc.strerror
         res = sedprog.run(text, value, delim)
+        if res.refused:
+            rt.err("%s: refusing to go on: the key path spliced into the sed program at line %d makes it %s\n"
+                   % (self.program, lineno, res.refused))
+            raise ScriptExit(2)
         if not res.ok:
             rt.err(res.error)        # a program sed rejects is reported before it opens any input
             return
