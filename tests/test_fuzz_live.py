@@ -245,3 +245,39 @@ def test_property_fuzzed_tables(ref_root, block):
         elif res[0].diff(res[1]):
             bad.append((seed, res[0].diff(res[1]), sc.to_json()))
     assert bad == []
+
+
+# --- NUL bytes, control characters and stray high bytes in what the tools print ----------------
+def _inject(r, text):
+    if not text:
+        return text
+    k = r.randint(0, len(text))
+    return text[:k] + r.choice(["\0", "\0\0", "\x01", "\udcff", "\r"]) + text[k:]
+
+
+def make_binary(seed: int) -> Scenario:
+    import dataclasses
+    sc = make_wide(seed)
+    r = random.Random(seed * 13 + 5)
+    kw = {}
+    for field in ("networks", "packages", "triton_env"):
+        if r.random() < 0.35:
+            kw[field] = _inject(r, getattr(sc, field))
+    if r.random() < 0.3:
+        kw["master_ip"] = _inject(r, sc.master_ip or "10.0.0.1")
+    if r.random() < 0.3:
+        kw["env_id"] = _inject(r, sc.env_id or "1a7")
+    if r.random() < 0.4:
+        kw["curl_seq"] = [_inject(r, b) for b in (sc.curl_seq or ["starting\n", "kubernetes\n"])]
+    if r.random() < 0.4:
+        kw["ssh_ps"] = {k: _inject(r, v) for k, v in (sc.ssh_ps or {"10.0.1.1": _PS[0]}).items()}
+    if r.random() < 0.3:
+        kw["keygen"] = {k: _inject(r, v) for k, v in sc.keygen.items()}
+    if r.random() < 0.2:
+        kw["date_seq"] = [_inject(r, d) for d in (sc.date_seq or ["1500000000"])]
+    return dataclasses.replace(sc, **kw)
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_binary_output(ref_root, block):
+    assert _sweep(ref_root, make_binary, range(15 * block, 15 * (block + 1))) == []

@@ -148,3 +148,18 @@ def test_plain_assignment_has_no_brace_expansion():
     shell, env = {}, {}
     apply_triton_env("A={a,b}\n", shell, env)
     assert shell == {"A": "{a,b}"} and env == {}
+
+
+def test_a_command_that_does_not_exist_gets_bashs_answer():
+    """Nothing would run, so nothing needs refusing: `exp\\xffort X=1` is `command not found`,
+    labelled with the line of the eval text it stands on (the eval is at setup.sh:210)."""
+    from tritonk8ssupervisor_b200.tritonenv import CommandNotFound, ansic_quote
+    with pytest.raises(CommandNotFound) as exc:
+        apply_triton_env('export A="1"\n\nnosuchcommand_zz --flag\n', {}, {}, exists=lambda name: False)
+    assert str(exc.value) == "nosuchcommand_zz: command not found" and exc.value.line == 2
+    assert ansic_quote("exp\udcffort") == "$'exp\\377ort'" and ansic_quote("unse\rt") == "$'unse\\rt'"
+    # a command that exists, a builtin, a function of the script, a path: refused, never looked at further
+    for text in ("ls\n", "echo hi\n", "cleanRunner\n", "./x\n", "eval x\n"):
+        with pytest.raises(TritonEnvError) as exc:
+            apply_triton_env(text, {}, {}, exists=lambda name: name == "ls")
+        assert not isinstance(exc.value, CommandNotFound), text

@@ -268,6 +268,12 @@ EDGE: List[Scenario] = [
              note="ssh failures while counting are swallowed by '|| true'"),
     Scenario(name="wait_curl_fails", stdin=BLANK8 + YES, fail={"curl---connect-timeout": 7},
              note="cRetVal=$(curl …) under errexit: a refused connection ends the script with curl's status"),
+    Scenario(name="wait_binary_output_from_tools", stdin=_answers("", "", "", "", "2", "", "", "", "yes"),
+             curl_seq=["starting\x00\n", "503 Service Unavailable\x00\n", "503 Service Unavailable\n", "kubernetes\n"],
+             ssh_ps={"10.0.1.1": _PS_TWO_DASHBOARDS + "\x00\n", "10.0.1.2": "\x01\x1b \x7f k8s_kubernetes-dashboard.z\n" + _PS_TWO_DASHBOARDS},
+             note="a NUL byte makes the input a binary file for grep: no lines, 'binary file matches' on stderr instead -- so "
+                  "node 1's containers are not counted; $(...) drops NULs with a warning; wc -w counts only words that hold a "
+                  "printable character"),
     # --- clean (setup.sh:484-521) ----------------------------------------------
     Scenario(name="clean_fresh_yes", args=["-c"], stdin="yes\n", note="nothing to clean: still rewrites ansible.cfg"),
     Scenario(name="clean_fresh_no", args=["-c"], stdin="no\n", note="decline: exit 0"),
@@ -355,6 +361,13 @@ EDGE += [
              triton_env=triton_env_text() + "export i network\nexport master yn\nunset yn\n",
              note="`export NAME` before NAME has a value: it is exported the moment the script assigns it (the loop "
                   "counter i reaches terraform as i=3); unset takes the attribute away again"),
+    Scenario(name="triton_env_garbled_command", stdin=BLANK8 + YES,
+             triton_env='export SDC_URL="u"\nexp\udcffort SDC_ACCOUNT="a"\nexport SDC_KEY_ID="%s"\n' % DEFAULT_KEY_ID,
+             note="a byte flipped in `export`: for eval that is a command name; it does not exist, so nothing runs -- bash's "
+                  "`command not found` (the name in $'...' quoting, the line counted from the eval at 210), status 127"),
+    Scenario(name="triton_env_invalid_identifier", stdin=BLANK8 + YES,
+             triton_env='export SDC_URL="u"\nexport SDC-ACCOUNT="a" 2nd=x\nexport SDC_KEY_ID="%s"\n' % DEFAULT_KEY_ID,
+             note="export rejects the word itself: `not a valid identifier`, status 1, and errexit ends the run"),
     Scenario(name="triton_env_unsets_pwd", stdin=BLANK8 + YES, triton_env=triton_env_text() + "unset PWD OLDPWD\n",
              note="unset takes the export attribute with it: `cd` goes on working (from bash's own idea of the directory) and "
                   "sets both variables again, but terraform and ansible no longer find them in their environment"),

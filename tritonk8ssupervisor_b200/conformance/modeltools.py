@@ -70,6 +70,12 @@ class ModelRuntime(Runtime):
             raise RuntimeError("more than %d reads in one run: runaway prompt loop" % self.max_calls)
         return bashsem.read_builtin(self._next_byte)
 
+    def command_exists(self, name: str) -> bool:
+        from .sandbox import STUB_TOOLS
+        if name in STUB_TOOLS:
+            return name not in self.sc.missing_tools
+        return super().command_exists(name)
+
     # -- clock -------------------------------------------------------------
     def sleep(self, seconds: int, where: str = "") -> int:
         return self.run(["sleep", str(seconds)], where=where)[0]

@@ -91,6 +91,16 @@ class Runtime:
         with open(self.path(rel), "ab") as fh:
             fh.write(bashsem.to_bytes(text))
 
+    def command_exists(self, name: str) -> bool:
+        """Would bash find ``name`` on PATH (as an executable, or at least as a file)?"""
+        try:
+            find_command(name, self.env.get("PATH"), self.root)
+        except FileNotFoundError:
+            return False
+        except PermissionError:
+            return True
+        return True
+
     def passwd_home(self) -> str:
         """The user's home directory according to the password database: what
         bash expands ``~`` to when ``HOME`` is unset (setup.sh:216-217)."""

@@ -46,7 +46,7 @@ from . import sedprog
 from . import textops as tx
 from .basharith import ArithAbort, ArithError, ArithFatal, ArithRefused, Evaluator
 from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
-from .tritonenv import TritonEnvError, apply_triton_env
+from .tritonenv import CommandNotFound, InvalidIdentifier, TritonEnvError, apply_triton_env
 
 RULE = "#" * 80
 DASHES = "---------------"
@@ -251,13 +251,25 @@ class Supervisor:
         self.rt.err("%s: %s: %s\n" % (where, rel, exc.strerror))
         raise ScriptExit(1)
 
-    def cat_subst(self, rel: str) -> str:
+    def subst(self, output: str, lineno: int) -> str:
+        """``$(...)`` around something whose output is data: trailing newlines go, and so
+        do NUL bytes -- those with bash's warning, labelled with the reference line."""
+        if "\x00" in output:
+            self.rt.err("%s: warning: command substitution: ignored null byte in input\n" % self.at(lineno))
+        return sh.cmdsubst(output)
+
+    def cat_subst(self, rel: str, lineno: int = 0) -> str:
         """``$(cat rel)``; a missing file costs a message on stderr, not the run."""
         try:
-            return sh.cmdsubst(self.rt.read_text(rel))
+            text = self.rt.read_text(rel)
+            return self.subst(text, lineno) if lineno else sh.cmdsubst(text)
         except OSError as exc:
             self.rt.err("cat: %s: %s\n" % (rel, exc.strerror))
             return ""
+
+    def _binary_matches(self) -> None:
+        """What grep says instead of printing lines of input that holds a NUL byte."""
+        self.rt.err("grep: (standard input): binary file matches\n")
 
     def at(self, line: int) -> str:
         """``setup.sh: line N`` -- how bash labels its own diagnostics."""
@@ -364,8 +376,8 @@ class Supervisor:
         self.banner("Running ansible tasks...", 46)
         self.run_ansible()
 
-        master = self.cat_subst("terraform/masters.ip")
-        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        master = self.cat_subst("terraform/masters.ip", 53)
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id", 53)
         self.echo("", lineno=49)
         self.echo("Congratulations, your Kubernetes cluster setup has been complete.", lineno=50)
         self.echo("", lineno=51)
@@ -376,11 +388,11 @@ class Supervisor:
         self.echo("", lineno=57)
         self.wait_for_dashboard()
         self.echo("", lineno=87)
-        master = self.cat_subst("terraform/masters.ip")
-        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        master = self.cat_subst("terraform/masters.ip", 88)
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id", 88)
         self.echo("----> Kubernetes dashboard is at http://%s:8080/r/projects/%s/kubernetes-dashboard:9090/" % (master, env_id), lineno=88)
-        master = self.cat_subst("terraform/masters.ip")
-        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id")
+        master = self.cat_subst("terraform/masters.ip", 89)
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id", 89)
         self.echo("----> Kubernetes CLI config is at http://%s:8080/env/%s/kubernetes/kubectl" % (master, env_id), lineno=89)
         self.echo("", lineno=90)
         self.echo("    CONGRATULATIONS, YOU HAVE CONFIGURED YOUR KUBERNETES ENVIRONMENT!", lineno=91)
@@ -416,7 +428,15 @@ class Supervisor:
         rt, v = self.rt, self.v
         _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210), lone_subst=True)  # status is swallowed by eval "$(...)"
         try:
-            apply_triton_env(sh.cmdsubst(text), v, rt.env, home=rt.passwd_home)
+            apply_triton_env(self.subst(text, 210), v, rt.env, home=rt.passwd_home, exists=rt.command_exists)
+        except CommandNotFound as exc:
+            rt.err("%s: %s\n" % (self.at(210 + exc.line), exc))
+            raise ScriptExit(127)
+        except InvalidIdentifier as exc:
+            # bash's own verdict, not a refusal: eval numbers the lines of its text from the line it stands on
+            for message in exc.messages():
+                rt.err("%s: %s\n" % (self.at(210 + exc.line), message))
+            raise ScriptExit(1)
         except TritonEnvError as exc:
             rt.err("%s: %s\n" % (self.program, exc))
             raise ScriptExit(2)
@@ -438,7 +458,7 @@ class Supervisor:
             # tilde expansion yields quoted text: never split, never globbed
             key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], rt.root)
             _, out = rt.run(["ssh-keygen", "-E", "md5", "-lf"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
-            fp = sh.cmdsubst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""))
+            fp = self.subst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""), 217)
             matched_at = 218
             if fp == key_id:
                 found = True
@@ -446,9 +466,9 @@ class Supervisor:
                 matched_at = 225
                 # ssh-keygen too old for -E prints MD5 by default (setup.sh:222-229)
                 _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
-                if sh.cmdsubst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256")) == "":
+                if self.subst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256", binary=self._binary_matches), 223) == "":
                     _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
-                    if sh.cmdsubst(tx.awk_print_field(out, 2)) == key_id:
+                    if self.subst(tx.awk_print_field(out, 2), 224) == key_id:
                         found = True
             if found:
                 self.append_line("config", 'SDC_KEY="~/.ssh/%s"' % stem, matched_at)
@@ -496,8 +516,8 @@ class Supervisor:
         squeezed, blanks turned into '=', sorted (setup.sh:257,259)."""
         text = self._triton_table(argv, 259 if kvm_only else 257)
         if kvm_only:
-            text = tx.grep(text, r"-kvm-")
-        text = tx.grep(text, r"^NAME.*ID$", invert=True)
+            text = tx.grep(text, r"-kvm-", binary=self._binary_matches)
+        text = tx.grep(text, r"^NAME.*ID$", invert=True, binary=self._binary_matches)
         return sh.cmdsubst(tx.sort_lines(tx.tr(tx.tr_squeeze_spaces(text), " ", "=")))
 
     def _triton_table(self, argv: List[str], line: int) -> str:
@@ -708,8 +728,8 @@ class Supervisor:
             for index in self.args_of(values):
                 self.subshell_set("network", index)   # what `triton` finds in its environment if `network` is exported
                 text = self._triton_table(TRITON_NETWORKS, 536)
-                rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True)
-                acc = acc + "," + sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, index)))
+                rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True, binary=self._binary_matches)
+                acc = acc + "," + self.subst(tx.awk_last_field_if_many(self._nth_row(rows, index)), 536)
                 self.v["networks"] = acc
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
         return sh.cmdsubst(tx.sed_sub(t, r"^(.*),$", r"\1"))
@@ -717,9 +737,9 @@ class Supervisor:
     def package_id(self, args: List[str]) -> str:
         arg1 = args[0] if args else ""
         text = self._triton_table(TRITON_PACKAGES, 541)
-        rows = tx.grep(tx.grep(text, r"-kvm-"), r"^NAME.*ID$", invert=True)
+        rows = tx.grep(tx.grep(text, r"-kvm-", binary=self._binary_matches), r"^NAME.*ID$", invert=True, binary=self._binary_matches)
         rows = tx.sort_lines(tx.tr_squeeze_spaces(rows))
-        picked = sh.cmdsubst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)))
+        picked = self.subst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)), 541)
         return sh.cmdsubst(sh.echo_builtin([picked]))
 
     def _nth_row(self, rows: str, index: str) -> str:
@@ -935,7 +955,7 @@ class Supervisor:
         except OSError as exc:
             rt.err("tail: error reading 'terraform/masters.ip': %s\n" % exc.strerror)
             raise ScriptExit(1)                 # master=$(tail ...): the assignment has tail's status, errexit
-        master = v["master"] = sh.cmdsubst(last)
+        master = v["master"] = self.subst(last, 128)
         try:
             rt.write_text(vars_yml, sh.echo_builtin(["master: %s" % master]))
         except OSError as exc:
@@ -1031,17 +1051,17 @@ class Supervisor:
     # ------------------------------------------------------------------
     # dashboard wait loop  (setup.sh:59-85)
     # ------------------------------------------------------------------
-    def _dashboard_url_words(self) -> List[str]:
+    def _dashboard_url_words(self, line: int = 0) -> List[str]:
         """``http://$(cat terraform/masters.ip):8080/r/projects/$(cat …id)/kubernetes-dashboard:9090/``
         as an unquoted word."""
         return sh.expand_word([
-            ("http://", False), (self.cat_subst("terraform/masters.ip"), True),
-            (":8080/r/projects/", False), (self.cat_subst("ansible/tmp/kubernetes_environment.id"), True),
+            ("http://", False), (self.cat_subst("terraform/masters.ip", line), True),
+            (":8080/r/projects/", False), (self.cat_subst("ansible/tmp/kubernetes_environment.id", line), True),
             ("/kubernetes-dashboard:9090/", False)], self.rt.root)
 
     def _curl_dashboard(self, line: int) -> Tuple[int, str]:
         # cRetVal=$(curl ...) at :66 holds curl alone; at :74 curl heads a pipeline
-        return self.rt.run(["curl", "--connect-timeout", "5", "--max-time", "5", "-s"] + self._dashboard_url_words(),
+        return self.rt.run(["curl", "--connect-timeout", "5", "--max-time", "5", "-s"] + self._dashboard_url_words(line),
                            stdout=CAPTURE, where=self.at(line), lone_subst=line == 66)
 
     def _ssh_docker_ps(self, node: str, line: int) -> str:
@@ -1064,33 +1084,33 @@ class Supervisor:
             # expression.  Zero -- or an expression bash cannot evaluate -- means "poll now".
             date_status, now = rt.epoch(self.at(64))
             v["_"] = "1"                               # last argument of `sleep 1`
-            remainder = self.arith_eval("%s %% 15" % sh.cmdsubst(now), 64, "((", date_status)
+            remainder = self.arith_eval("%s %% 15" % self.subst(now, 64), 64, "((", date_status)
             if remainder is not None and remainder != 0:
                 continue
             v["DASHBOARD_CONTAINER_COUNT"] = "0"
             status, body = self._curl_dashboard(66)
             self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
-            v["cRetVal"] = sh.cmdsubst(body)
+            v["cRetVal"] = self.subst(body, 66)
             shown = sh.echo_unquoted(v["cRetVal"], rt.root)
-            if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True)) != 0:
+            if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True, binary=self._binary_matches)) != 0:
                 up = True
                 v["KUBERNETES_DASHBOARD_UP"] = "true"
                 continue
             count = 0
-            for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
+            for node in self.args_of(self.cat_subst("terraform/hosts.ip", 71)):
                 v["node"] = node
-                ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard")
+                ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard", binary=self._binary_matches)
                 count += tx.wc_w(tx.awk_print_field(ps, 1))
                 v["DASHBOARD_CONTAINER_COUNT"] = str(count)
             if count != 2:
                 continue
             _, body = self._curl_dashboard(74)
-            if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True)) == 0:
+            if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True, binary=self._binary_matches)) == 0:
                 continue
-            for node in self.args_of(self.cat_subst("terraform/hosts.ip")):
+            for node in self.args_of(self.cat_subst("terraform/hosts.ip", 75)):
                 v["node"] = node
-                ps = tx.grep(self._ssh_docker_ps(node, 76), r"k8s_POD.*dashboard")
-                container = v["dashboard_container"] = sh.cmdsubst(tx.awk_print_field(ps, 1))
+                ps = tx.grep(self._ssh_docker_ps(node, 76), r"k8s_POD.*dashboard", binary=self._binary_matches)
+                container = v["dashboard_container"] = self.subst(tx.awk_print_field(ps, 1), 76)
                 if container != "":
                     status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,
                                         "docker stop -t0 %s" % container], stdout=DEVNULL, stderr=DEVNULL)
@@ -1140,7 +1160,7 @@ class Supervisor:
                     recorded += rt.read_text(rel)
                 except OSError as exc:
                     rt.err("cat: %s: %s\n" % (rel, exc.strerror))
-            recorded = sh.cmdsubst(recorded)
+            recorded = self.subst(recorded, 505)
             for host_key in self.args_of(recorded):
                 self.v["host_key"] = host_key
                 # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped

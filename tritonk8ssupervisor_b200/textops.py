@@ -9,7 +9,7 @@ reference uses are covered (cited per function).
 from __future__ import annotations
 
 import re
-from typing import List
+from typing import Callable, List, Optional
 
 from .bashsem import c_sort_key
 
@@ -28,10 +28,18 @@ def unlines(ls: List[str]) -> str:
     return "".join(l + "\n" for l in ls)
 
 
-def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = False) -> str:
-    """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE."""
+def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = False,
+         binary: Optional[Callable[[], None]] = None) -> str:
+    """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE.  Input that holds a
+    NUL byte is a binary file to grep: it prints no line, and if one would have been selected it says
+    ``grep: (standard input): binary file matches`` on stderr instead -- ``binary()`` is called then."""
     rx = re.compile(pattern, re.I if ignore_case else 0)
-    return unlines([l for l in lines(text) if (rx.search(l) is not None) != invert])
+    selected = [l for l in lines(text) if (rx.search(l) is not None) != invert]
+    if "\0" in text:
+        if selected and binary is not None:
+            binary()
+        return ""
+    return unlines(selected)
 
 
 def tr_squeeze_spaces(text: str) -> str:
@@ -124,5 +132,13 @@ def wc_l(text: str) -> int:
 
 
 def wc_w(text: str) -> int:
-    """``wc -w``."""
-    return len([w for w in re.split(r"[ \t\n\r\f\v]+", text) if w])
+    """``wc -w`` in the C locale: a word is a run of non-blank bytes holding at least one
+    printable one; control and high bytes neither start a word nor end one."""
+    count, in_word = 0, False
+    for b in text.encode("utf-8", "surrogateescape"):
+        if b in b" \t\n\r\f\v":
+            in_word = False
+        elif 0x20 < b < 0x7F and not in_word:
+            in_word = True
+            count += 1
+    return count

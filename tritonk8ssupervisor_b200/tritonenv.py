@@ -23,6 +23,49 @@ class TritonEnvError(ValueError):
     pass
 
 
+class CommandNotFound(TritonEnvError):
+    """The text names a command that does not exist: nothing would run, bash says
+    ``NAME: command not found`` (status 127, which errexit makes the script's)."""
+
+    def __init__(self, name: str, line: int):
+        super().__init__("%s: command not found" % ansic_quote(name))
+        self.name, self.line = name, line
+
+
+#: words bash does not look up on PATH: builtins, keywords, and the functions of setup.sh
+_SHELL_WORDS = frozenset((
+    ". : [ alias bg bind break builtin caller cd command compgen complete compopt continue declare dirs disown echo enable "
+    "eval exec exit export false fc fg getopts hash help history jobs kill let local logout mapfile popd printf pushd pwd read "
+    "readarray readonly return set shift shopt source suspend test times trap true type typeset ulimit umask unalias unset wait "
+    "if then else elif fi case esac for select while until do done in function time { } ! [[ ]] coproc "
+    "main getArgument runAnsible createAnsibleConfigs runTerraformTasks updateTerraformConfig setConfigToFile "
+    "setConfigFromTritonENV setVarDefaults getConfigFromUser verifyConfig cleanRunner debugVars getNetworkIDs getPackageID "
+    "exportVars").split())
+
+
+def ansic_quote(text: str) -> str:
+    """How bash prints a word that holds non-printable bytes: ``$'exp\\377ort'``."""
+    data = text.encode("utf-8", "surrogateescape")
+    if all(0x20 <= b < 0x7F for b in data):
+        return text
+    names = {7: "\\a", 8: "\\b", 27: "\\E", 12: "\\f", 10: "\\n", 13: "\\r", 9: "\\t", 11: "\\v", 92: "\\\\", 39: "\\'"}
+    return "$'" + "".join(names.get(b) or (chr(b) if 0x20 <= b < 0x7F else "\\%03o" % b) for b in data) + "'"
+
+
+class InvalidIdentifier(TritonEnvError):
+    """``export WORD`` where WORD is no ``NAME[=value]``: not a refusal -- bash itself
+    rejects it (``export: `WORD': not a valid identifier``, status 1, which errexit makes
+    the script's).  ``line`` is the 0-based line of the text the command started on."""
+
+    def __init__(self, words: List[str], line: int):
+        super().__init__("; ".join("export: `%s': not a valid identifier" % w for w in words))
+        #: every word of the command that was rejected (the valid ones have taken effect)
+        self.words, self.line = words, line
+
+    def messages(self) -> List[str]:
+        return ["export: `%s': not a valid identifier" % w for w in self.words]
+
+
 #: variables that change how bash reads the *rest of the script* (field splitting,
 #: globbing, locale of its pattern matching and of sort/grep/sed).  `eval` would let
 #: `triton env` set them; the path here is written for their default values.
@@ -66,10 +109,12 @@ def _parameter(text: str, i: int, quoted: bool) -> Tuple[Optional[_Var], int]:
     return None, i + 1
 
 
-def _split_commands(text: str) -> List[List[List[_Piece]]]:
+def _split_commands(text: str) -> Tuple[List[List[List[_Piece]]], List[int]]:
     """Tokenise into commands (newline or ';' separated), each a list of words,
-    honouring single quotes, double quotes and backslashes."""
+    honouring single quotes, double quotes and backslashes.  Also returns, per
+    command, the 0-based line of the text it starts on."""
     cmds: List[List[List[_Piece]]] = []
+    cmd_lines: List[int] = []
     words: List[List[_Piece]] = []
     cur: List[_Piece] = []
     have_word = False
@@ -87,6 +132,7 @@ def _split_commands(text: str) -> List[List[List[_Piece]]]:
         end_word()
         if words:
             cmds.append(words)
+            cmd_lines.append(text.count("\n", 0, i) - sum(1 for w in words for p in w if not isinstance(p, _Var) and p[0] == "\n"))
         words = []
 
     while i < n:
@@ -153,7 +199,7 @@ def _split_commands(text: str) -> List[List[List[_Piece]]]:
             have_word = True
             i += 1
     end_cmd()
-    return cmds
+    return cmds, cmd_lines
 
 
 def _default_home() -> str:
@@ -220,10 +266,12 @@ def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[
 
 
 def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
-                     home: Optional[Callable[[], str]] = None) -> None:
+                     home: Optional[Callable[[], str]] = None,
+                     exists: Optional[Callable[[str], bool]] = None) -> None:
     """Mutate ``shell_vars`` (all shell variables) and ``env`` (the exported
     ones) as ``eval`` of ``text`` would for the supported dialect.  ``home()``
-    is what ``~`` stands for when ``HOME`` is not among the shell variables."""
+    is what ``~`` stands for when ``HOME`` is not among the shell variables;
+    ``exists(name)`` says whether a command of that name can be found on PATH."""
     def tilde_home() -> str:
         if "HOME" in shell_vars:
             return shell_vars["HOME"]
@@ -238,16 +286,21 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
     pending = getattr(shell_vars, "export_when_set", None)
     if pending is None:
         pending = set()         # a plain dict: the attribute is remembered for the rest of this text at least
-    for words in _split_commands(text):
+    commands, lines = _split_commands(text)
+    for words, line in zip(commands, lines):
         head = plain(words[0]) if not any(isinstance(p, _Var) for p in words[0]) else None
         if head == "export":
             if len(words) == 1:
                 # a bare `export` lists every exported variable on the script's stdout
                 raise TritonEnvError("refusing to run a bare `export` from `triton env` output")
+            rejected: List[str] = []
             for w in words[1:]:
                 parsed = _assignment(w, shell_vars, tilde_home)
                 if parsed is None:
-                    raise TritonEnvError("not a valid identifier in `triton env` output: %r" % _show(w))
+                    if any(isinstance(p, _Var) for p in w):
+                        raise TritonEnvError("not a valid identifier in `triton env` output: %r" % _show(w))
+                    rejected.append(_show(w))
+                    continue
                 name, value = parsed
                 _guard(name)
                 if value is not None:
@@ -256,6 +309,8 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                     env[name] = shell_vars[name]
                 else:
                     pending.add(name)           # `export NAME` before NAME has a value: exported once it gets one
+            if rejected:
+                raise InvalidIdentifier(rejected, line)
         elif head == "unset":
             for w in words[1:]:
                 name = plain(w)
@@ -266,6 +321,12 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
         else:
             parsed = _assignment(words[0], shell_vars, tilde_home) if len(words) == 1 else None
             if parsed is None or parsed[1] is None:
+                # a command.  One that cannot be found runs nothing, and bash's answer to it can be
+                # given without running anything; every other command is refused.
+                if (exists is not None and head is not None and head != "" and "/" not in head and "=" not in head
+                        and head not in _SHELL_WORDS and all(not isinstance(p, _Var) for w in words for p in w)
+                        and not exists(head)):
+                    raise CommandNotFound(head, line)
                 raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(_show(w) for w in words))
             name, value = parsed
             _guard(name)
