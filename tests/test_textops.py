@@ -65,3 +65,19 @@ def test_against_real_tool_fixed(idx):
 def test_against_real_tools_random(text):
     for ours, argv in CASES:
         assert ours(text) == real(argv, text), (argv, text)
+
+
+def test_grep_in_a_utf8_locale_holds_back_what_is_no_text():
+    """LANG=C.UTF-8: a selected line that is not valid UTF-8 is not printed (the others are),
+    `.` does not match such a byte, and a NUL byte anywhere silences grep altogether."""
+    env = {"PATH": "/usr/bin:/bin", "LANG": "C.UTF-8"}
+    cases = [("a=1\n\nb=\udcffx\nc=3\nd=\udcff\ne=5\n", ["grep", "-v", "^$"], dict(pattern=r"^$", invert=True)),
+             ("NAME  \udcff ID\nNAME   ID\nx y\n", ["grep", "-v", "^NAME.*ID$"], dict(pattern=r"^NAME.*ID$", invert=True)),
+             ("kubernetes \udcff\nkubernetes\n", ["grep", "-i", "kubernetes"], dict(pattern=r"kubernetes", ignore_case=True)),
+             ("a\x00b\nc\n", ["grep", "c"], dict(pattern=r"c")),
+             ("plain\ntext\n", ["grep", "t"], dict(pattern=r"t"))]
+    for text, argv, kw in cases:
+        p = subprocess.run(argv, input=to_bytes(text), capture_output=True, env=env)
+        said = []
+        assert tx.grep(text, utf8=True, binary=lambda: said.append(1), **kw) == from_bytes(p.stdout), argv
+        assert bool(said) == (b"binary file matches" in p.stderr), argv

@@ -432,6 +432,12 @@ EDGE += [
     # --- the operator's environment -----------------------------------------------------------
     Scenario(name="env_lang_utf8_no_lc_all", stdin=_answers("caf\u00e9 \u2615", "", "", "", "", "2,1", "", "", "yes"),
              env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"], note="LANG=C.UTF-8 with LC_ALL unset: same bytes, same order"),
+    Scenario(name="env_utf8_bytes_that_are_no_characters", stdin=_answers("ok", "bad \udcff byte", "", "", "2", "", "", "", "yes"),
+             env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"],
+             networks=triton_table(DOC_NETWORKS).replace("NAME  ", "NAME \udcff", 1),
+             note="in a UTF-8 locale grep holds back lines that are not valid UTF-8 ('binary file matches'): the description "
+                  "never reaches config.tmp and is not exported; `.` does not match such a byte, so the header row survives "
+                  "grep -v '^NAME.*ID$' only to be held back as well"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

@@ -30,7 +30,7 @@ printf '%s|%s|%s\n' "$tool" "$rel" "$*" >> "$S/calls.log"
 # of it.  Left out: this stub's own plumbing, and PYTHON* (how the test harness
 # makes an uninstalled Python package importable).
 sbx=${S%/state}
-envdump() { env | grep -v -E '^(TK8S_STUB_|PYTHON)' | LC_ALL=C sort | sed "s|$sbx|<SBX>|g"; }
+envdump() { env | LC_ALL=C grep -a -v -E '^(TK8S_STUB_|PYTHON)' | LC_ALL=C sort | LC_ALL=C sed "s|$sbx|<SBX>|g"; }
 case "$tool" in
     terraform|ansible-playbook) envdump | sed 's/^/  env:/' >> "$S/calls.log" ;;
     *) printf '  env~:%s\n' "$(envdump | md5sum | cut -c1-12)" >> "$S/calls.log" ;;
@@ -125,13 +125,13 @@ terraform)
             [ -f "$S/master_ip" ] && master_ip=$(cat "$S/master_ip")
             i=0
             # one IP per module block, in file order, the way local-exec appends them
-            grep 'source = ' rancher.tf | while read -r _ _ src; do
+            LC_ALL=C grep -a 'source = ' rancher.tf | while read -r _ _ src; do
                 case "$src" in
                     '"master"') echo "$master_ip" >> masters.ip ;;
                     '"host"') i=$((i + 1)); echo "10.0.1.$i" >> hosts.ip ;;
                 esac
             done
-            echo "Apply complete! Resources: $(grep -c 'source = ' rancher.tf) added, 0 changed, 0 destroyed."
+            echo "Apply complete! Resources: $(LC_ALL=C grep -a -c 'source = ' rancher.tf) added, 0 changed, 0 destroyed."
             ;;
         destroy)
             echo "Destroy complete!"

@@ -91,6 +91,22 @@ class Runtime:
         with open(self.path(rel), "ab") as fh:
             fh.write(bashsem.to_bytes(text))
 
+    def utf8_locale(self) -> bool:
+        """Is the character set of the locale the children will run in UTF-8?  (LC_ALL, else
+        LC_CTYPE, else LANG; a locale that is not installed counts as C, as it does for them.)"""
+        name = self.env.get("LC_ALL") or self.env.get("LC_CTYPE") or self.env.get("LANG") or ""
+        if name in ("", "C", "POSIX"):
+            return False
+        import locale
+        saved = locale.setlocale(locale.LC_CTYPE)
+        try:
+            locale.setlocale(locale.LC_CTYPE, name)
+            return locale.nl_langinfo(locale.CODESET).upper().replace("-", "") == "UTF8"
+        except locale.Error:
+            return False
+        finally:
+            locale.setlocale(locale.LC_CTYPE, saved)
+
     def command_exists(self, name: str) -> bool:
         """Would bash find ``name`` on PATH (as an executable, or at least as a file)?"""
         try:

@@ -96,6 +96,8 @@ class Supervisor:
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
         self._shell_bookkeeping()
+        #: the character set of the locale is UTF-8: grep then takes bytes that are not valid UTF-8 for binary data
+        self.utf8 = rt.utf8_locale()
         self._tables: Dict[tuple, str] = {}
         self._lineno = 0
         self._scopes: List[Dict[str, tuple]] = []
@@ -267,9 +269,9 @@ class Supervisor:
             self.rt.err("cat: %s: %s\n" % (rel, exc.strerror))
             return ""
 
-    def _binary_matches(self) -> None:
-        """What grep says instead of printing lines of input that holds a NUL byte."""
-        self.rt.err("grep: (standard input): binary file matches\n")
+    def _binary_matches(self, name: str = "(standard input)") -> None:
+        """What grep says instead of printing lines of input it takes for a binary file."""
+        self.rt.err("grep: %s: binary file matches\n" % name)
 
     def at(self, line: int) -> str:
         """``setup.sh: line N`` -- how bash labels its own diagnostics."""
@@ -466,7 +468,7 @@ class Supervisor:
                 matched_at = 225
                 # ssh-keygen too old for -E prints MD5 by default (setup.sh:222-229)
                 _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
-                if self.subst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256", binary=self._binary_matches), 223) == "":
+                if self.subst(tx.grep(tx.awk_print_field(out, 2), r"^SHA256", binary=self._binary_matches, utf8=self.utf8), 223) == "":
                     _, out = rt.run(["ssh-keygen", "-l", "-f"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
                     if self.subst(tx.awk_print_field(out, 2), 224) == key_id:
                         found = True
@@ -516,8 +518,8 @@ class Supervisor:
         squeezed, blanks turned into '=', sorted (setup.sh:257,259)."""
         text = self._triton_table(argv, 259 if kvm_only else 257)
         if kvm_only:
-            text = tx.grep(text, r"-kvm-", binary=self._binary_matches)
-        text = tx.grep(text, r"^NAME.*ID$", invert=True, binary=self._binary_matches)
+            text = tx.grep(text, r"-kvm-", binary=self._binary_matches, utf8=self.utf8)
+        text = tx.grep(text, r"^NAME.*ID$", invert=True, binary=self._binary_matches, utf8=self.utf8)
         return sh.cmdsubst(tx.sort_lines(tx.tr(tx.tr_squeeze_spaces(text), " ", "=")))
 
     def _triton_table(self, argv: List[str], line: int) -> str:
@@ -728,7 +730,7 @@ class Supervisor:
             for index in self.args_of(values):
                 self.subshell_set("network", index)   # what `triton` finds in its environment if `network` is exported
                 text = self._triton_table(TRITON_NETWORKS, 536)
-                rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True, binary=self._binary_matches)
+                rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True, binary=self._binary_matches, utf8=self.utf8)
                 acc = acc + "," + self.subst(tx.awk_last_field_if_many(self._nth_row(rows, index)), 536)
                 self.v["networks"] = acc
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
@@ -737,7 +739,7 @@ class Supervisor:
     def package_id(self, args: List[str]) -> str:
         arg1 = args[0] if args else ""
         text = self._triton_table(TRITON_PACKAGES, 541)
-        rows = tx.grep(tx.grep(text, r"-kvm-", binary=self._binary_matches), r"^NAME.*ID$", invert=True, binary=self._binary_matches)
+        rows = tx.grep(tx.grep(text, r"-kvm-", binary=self._binary_matches, utf8=self.utf8), r"^NAME.*ID$", invert=True, binary=self._binary_matches, utf8=self.utf8)
         rows = tx.sort_lines(tx.tr_squeeze_spaces(rows))
         picked = self.subst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)), 541)
         return sh.cmdsubst(sh.echo_builtin([picked]))
@@ -811,12 +813,13 @@ class Supervisor:
         except OSError as exc:
             self._redirect_failed("config.tmp", exc, 544)
         try:
-            text = tx.grep(self.rt.read_text("config"), r"^$", invert=True)
+            raw = self.rt.read_text("config")
         except OSError as exc:
             self.rt.err("grep: config: %s\n" % exc.strerror)
             raise ScriptExit(2)
+        text = tx.grep(raw, r"^$", invert=True, utf8=self.utf8, binary=lambda: self._binary_matches("config"))
         self.rt.write_text("config.tmp", text)  # stays behind if an export fails (errexit)
-        if text == "":
+        if not any(line != "" for line in tx.lines(raw)):
             raise ScriptExit(1)                 # grep selected nothing: status 1, errexit
         # done <config.tmp: what is read back is what the file holds (a link to /dev/null holds nothing)
         data = sh.to_bytes(self.rt.read_text("config.tmp"))
@@ -1092,24 +1095,24 @@ class Supervisor:
             self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
             v["cRetVal"] = self.subst(body, 66)
             shown = sh.echo_unquoted(v["cRetVal"], rt.root)
-            if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True, binary=self._binary_matches)) != 0:
+            if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True, binary=self._binary_matches, utf8=self.utf8)) != 0:
                 up = True
                 v["KUBERNETES_DASHBOARD_UP"] = "true"
                 continue
             count = 0
             for node in self.args_of(self.cat_subst("terraform/hosts.ip", 71)):
                 v["node"] = node
-                ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard", binary=self._binary_matches)
+                ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard", binary=self._binary_matches, utf8=self.utf8)
                 count += tx.wc_w(tx.awk_print_field(ps, 1))
                 v["DASHBOARD_CONTAINER_COUNT"] = str(count)
             if count != 2:
                 continue
             _, body = self._curl_dashboard(74)
-            if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True, binary=self._binary_matches)) == 0:
+            if tx.wc_l(tx.grep(body, r"Service Unavailable", ignore_case=True, binary=self._binary_matches, utf8=self.utf8)) == 0:
                 continue
             for node in self.args_of(self.cat_subst("terraform/hosts.ip", 75)):
                 v["node"] = node
-                ps = tx.grep(self._ssh_docker_ps(node, 76), r"k8s_POD.*dashboard", binary=self._binary_matches)
+                ps = tx.grep(self._ssh_docker_ps(node, 76), r"k8s_POD.*dashboard", binary=self._binary_matches, utf8=self.utf8)
                 container = v["dashboard_container"] = self.subst(tx.awk_print_field(ps, 1), 76)
                 if container != "":
                     status, _ = rt.run(["ssh", "-o", "StrictHostKeyChecking=no", "root@%s" % node,

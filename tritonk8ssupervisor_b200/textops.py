@@ -29,16 +29,29 @@ def unlines(ls: List[str]) -> str:
 
 
 def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = False,
-         binary: Optional[Callable[[], None]] = None) -> str:
-    """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE.  Input that holds a
-    NUL byte is a binary file to grep: it prints no line, and if one would have been selected it says
-    ``grep: (standard input): binary file matches`` on stderr instead -- ``binary()`` is called then."""
+         binary: Optional[Callable[[], None]] = None, utf8: bool = False) -> str:
+    """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE.
+
+    What grep takes for binary data it does not print.  Input holding a NUL byte is binary as a
+    whole: no line comes out.  When the locale's character set is UTF-8 (``utf8``), a selected line
+    that is not valid UTF-8 is left out, the others are printed.  Either way grep says ``binary
+    file matches`` on stderr, once, if it held anything back -- ``binary()`` is called then."""
     rx = re.compile(pattern, re.I if ignore_case else 0)
-    selected = [l for l in lines(text) if (rx.search(l) is not None) != invert]
+
+    def hit(line: str) -> bool:
+        if utf8:
+            # a byte that is no character is matched by nothing, not even by `.`; Python's `.` stops at a newline
+            line = "".join("\n" if "\udc80" <= c <= "\udcff" else c for c in line)
+        return rx.search(line) is not None
+    selected = [l for l in lines(text) if hit(l) != invert]
+    held_back = False
     if "\0" in text:
-        if selected and binary is not None:
-            binary()
-        return ""
+        held_back, selected = bool(selected), []
+    elif utf8:
+        clean = [l for l in selected if not any("\udc80" <= c <= "\udcff" for c in l)]
+        held_back, selected = len(clean) != len(selected), clean
+    if held_back and binary is not None:
+        binary()
     return unlines(selected)
 
 
