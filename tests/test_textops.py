@@ -36,7 +36,7 @@ CASES = [
     (lambda t: tx.strip_dquotes(t), ["sed", 's/"//g']),
     (lambda t: tx.sed_sub(t, r"=", "  ", count=0), ["sed", "s/=/  /g"]),
     (lambda t: tx.sed_sub(t, r",", '","', count=0), ["sed", 's/,/","/g']),
-    (lambda t: tx.sed_sub(t, r"^(.*),$", r"\1"), ["sed", r"s/\(.*\),$/\1/"]),
+    (lambda t: tx.sed_sub(t, r"(.*),$", r"\1"), ["sed", r"s/\(.*\),$/\1/"]),
     (lambda t: tx.sed_sub(t, r"^,(.*)$", r"\1"), ["sed", r"s/^,\(.*\)$/\1/"]),
     (lambda t: tx.sed_sub(t, r".pub$", ""), ["sed", "s/.pub$//"]),
     (lambda t: tx.sed_print_line(t, 2), ["sed", "-n", "2p"]),
@@ -81,3 +81,15 @@ def test_grep_in_a_utf8_locale_holds_back_what_is_no_text():
         said = []
         assert tx.grep(text, utf8=True, binary=lambda: said.append(1), **kw) == from_bytes(p.stdout), argv
         assert bool(said) == (b"binary file matches" in p.stderr), argv
+
+
+def test_sed_in_a_utf8_locale_does_not_match_a_stray_byte_with_a_dot():
+    env = {"PATH": "/usr/bin:/bin", "LANG": "C.UTF-8"}
+    cases = [("x\udcffpub\nxapub\n.pub\n", ["sed", "s/.pub$//"], (r".pub$", "")),
+             ("1,\udcff,\n2,3,\n", ["sed", r"s/\(.*\),$/\1/"], (r"(.*),$", r"\1")),
+             (",a\udcff\n,b\n", ["sed", r"s/^,\(.*\)$/\1/"], (r"^,(.*)$", r"\1"))]
+    for text, argv, (pattern, repl) in cases:
+        p = subprocess.run(argv, input=to_bytes(text), capture_output=True, env=env)
+        assert tx.sed_sub(text, pattern, repl, utf8=True) == from_bytes(p.stdout), argv
+        c = subprocess.run(argv, input=to_bytes(text), capture_output=True, env=ENV)
+        assert tx.sed_sub(text, pattern, repl) == from_bytes(c.stdout), argv

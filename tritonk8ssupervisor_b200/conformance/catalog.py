@@ -438,6 +438,11 @@ EDGE += [
              note="in a UTF-8 locale grep holds back lines that are not valid UTF-8 ('binary file matches'): the description "
                   "never reaches config.tmp and is not exported; `.` does not match such a byte, so the header row survives "
                   "grep -v '^NAME.*ID$' only to be held back as well"),
+    Scenario(name="env_utf8_key_name_with_a_stray_byte", stdin=BLANK8 + YES, env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"],
+             ssh_files={"k\udcffpub": "K\n", "id_rsa": "K\n"}, keygen={"k\udcffpub": "2048 MD5:%s c (RSA)\n" % DEFAULT_KEY_ID},
+             keygen_sha={},
+             note="sed 's/.pub$//' in a UTF-8 locale: the dot does not match a byte that is no character, so 'k<ff>pub' keeps "
+                  "its name (in the C locale it would be asked about as 'k')"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

@@ -77,7 +77,7 @@ def _fail(pos: int, what: str) -> SedResult:
     return SedResult(False, error="sed: -e expression #1, char %d: %s\n" % (pos, what))
 
 
-def run(text: str, value: str, delim: str) -> SedResult:
+def run(text: str, value: str, delim: str, utf8: bool = False) -> SedResult:
     """Run ``s<d>private_key_file = .*$<d>private_key_file = VALUE<d>g`` over ``text``."""
     program_tail = value + delim + "g"
     # --- replacement: up to the first unescaped delimiter -----------------------
@@ -202,7 +202,8 @@ def run(text: str, value: str, delim: str) -> SedResult:
             return _fail(VALUE_AT + i, "unknown command: `%s'" % c)
 
     # --- execute ----------------------------------------------------------------------
-    rx = re.compile(REGEX, re.I if icase else 0)
+    # in a UTF-8 locale `.` does not match a byte that is no character
+    rx = re.compile(REGEX.replace(".", "[^\udc80-\udcff\n]") if utf8 else REGEX, re.I if icase else 0)
 
     def replacement(m: "re.Match[str]") -> str:
         return PREFIX + "".join(m.group(0) if k == "match" else t for k, t in parts)

@@ -455,7 +455,7 @@ class Supervisor:
         found = False
         for f in self.args_of(self._ls_ssh_dir()):
             # ~/.ssh/$(echo $f | sed 's/.pub$//') -- unquoted, so it can be several words
-            stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, rt.root), r".pub$", ""))
+            stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, rt.root), r".pub$", "", utf8=self.utf8))
             v["f"] = f                                 # the loop variable is a global of the script
             # tilde expansion yields quoted text: never split, never globbed
             key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], rt.root)
@@ -636,7 +636,7 @@ class Supervisor:
         """``echo $V | tr ',' '\\n' | sort | uniq | tr '\\n' ',' | sed 's/\\(.*\\),$/\\1/'``
         -- lexical sort: ``10,2`` stays ``10,2`` (setup.sh:333-334)."""
         t = tx.uniq(tx.sort_lines(tx.tr(sh.echo_unquoted(value, self.rt.root), ",", "\n")))
-        return sh.cmdsubst(tx.sed_sub(tx.tr(t, "\n", ","), r"^(.*),$", r"\1"))
+        return sh.cmdsubst(tx.sed_sub(tx.tr(t, "\n", ","), r"(.*),$", r"\1", utf8=self.utf8))
 
     def _out_of_range(self, items: List[str], count: int, var: str, lineno: int) -> int:
         """How many of ``items`` fall outside 1..count by
@@ -733,8 +733,8 @@ class Supervisor:
                 rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True, binary=self._binary_matches, utf8=self.utf8)
                 acc = acc + "," + self.subst(tx.awk_last_field_if_many(self._nth_row(rows, index)), 536)
                 self.v["networks"] = acc
-        t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1")
-        return sh.cmdsubst(tx.sed_sub(t, r"^(.*),$", r"\1"))
+        t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1", utf8=self.utf8)
+        return sh.cmdsubst(tx.sed_sub(t, r"(.*),$", r"\1", utf8=self.utf8))
 
     def package_id(self, args: List[str]) -> str:
         arg1 = args[0] if args else ""
@@ -1001,7 +1001,7 @@ class Supervisor:
             readable = True
         except OSError as exc:
             text, readable, why = "", False, exc.strerror
-        res = sedprog.run(text, value, delim)
+        res = sedprog.run(text, value, delim, utf8=self.utf8)
         if res.refused:
             rt.err("%s: refusing to go on: the key path spliced into the sed program at line %d makes it %s\n"
                    % (self.program, lineno, res.refused))

@@ -79,10 +79,19 @@ def uniq(text: str) -> str:
     return unlines(out)
 
 
-def sed_sub(text: str, pattern: str, repl, count: int = 1) -> str:
+#: what `.` matches when the locale's character set is UTF-8: any character, but not a byte that is none
+UTF8_DOT = "[^\udc80-\udcff\n]"
+
+
+def utf8_pattern(pattern: str) -> str:
+    """The same regular expression for a UTF-8 locale (unescaped dots only; the patterns of the path are that simple)."""
+    return re.sub(r"(?<!\\)\.", lambda m: UTF8_DOT, pattern)
+
+
+def sed_sub(text: str, pattern: str, repl, count: int = 1, utf8: bool = False) -> str:
     """``sed 's/PATTERN/REPL/[g]'`` line by line; ``count=0`` is the ``g`` flag.
     GNU sed keeps a missing final newline missing."""
-    rx = re.compile(pattern)
+    rx = re.compile(utf8_pattern(pattern) if utf8 else pattern)
     ls = text.split("\n")
     tail_nl = ls[-1] == ""
     if tail_nl:
