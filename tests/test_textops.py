@@ -93,3 +93,15 @@ def test_sed_in_a_utf8_locale_does_not_match_a_stray_byte_with_a_dot():
         assert tx.sed_sub(text, pattern, repl, utf8=True) == from_bytes(p.stdout), argv
         c = subprocess.run(argv, input=to_bytes(text), capture_output=True, env=ENV)
         assert tx.sed_sub(text, pattern, repl) == from_bytes(c.stdout), argv
+
+
+def test_wc_w_classifies_characters_as_the_locale_does():
+    import random
+    r = random.Random(2)
+    chars = ["é", "\udcff", "a", " ", "\xa0", " ", "​", "\x01", "日", "\t", "\x85", " ", "\x7f", "\udc80", "b", "\xad",
+             "", "\U0001F600", "　", " ", "\x1c", " ", "᠎"]
+    for _ in range(150):
+        text = "".join(r.choice(chars) for _ in range(r.randint(0, 8))) + "\n"
+        for env, utf8 in (({"LC_ALL": "C"}, False), ({"LANG": "C.UTF-8"}, True)):
+            real = int(subprocess.run(["wc", "-w"], input=to_bytes(text), capture_output=True, env=dict(env, PATH="/usr/bin:/bin")).stdout)
+            assert tx.wc_w(text, utf8=utf8) == real, (ascii(text), utf8)

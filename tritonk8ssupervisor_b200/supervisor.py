@@ -1103,7 +1103,7 @@ class Supervisor:
             for node in self.args_of(self.cat_subst("terraform/hosts.ip", 71)):
                 v["node"] = node
                 ps = tx.grep(self._ssh_docker_ps(node, 72), r"kubernetes-dashboard", binary=self._binary_matches, utf8=self.utf8)
-                count += tx.wc_w(tx.awk_print_field(ps, 1))
+                count += tx.wc_w(tx.awk_print_field(ps, 1), utf8=self.utf8)
                 v["DASHBOARD_CONTAINER_COUNT"] = str(count)
             if count != 2:
                 continue

@@ -9,6 +9,7 @@ reference uses are covered (cited per function).
 from __future__ import annotations
 
 import re
+import unicodedata
 from typing import Callable, List, Optional
 
 from .bashsem import c_sort_key
@@ -153,14 +154,16 @@ def wc_l(text: str) -> int:
     return text.count("\n")
 
 
-def wc_w(text: str) -> int:
-    """``wc -w`` in the C locale: a word is a run of non-blank bytes holding at least one
-    printable one; control and high bytes neither start a word nor end one."""
+def wc_w(text: str, utf8: bool = False) -> int:
+    """``wc -w``: a word is a run of non-blank characters holding at least one printable
+    one; what is neither (control characters, bytes that are no character) starts no word
+    and ends none.  In the C locale only ASCII is printable; in a UTF-8 locale (``utf8``)
+    the characters beyond it are classified too."""
     count, in_word = 0, False
-    for b in text.encode("utf-8", "surrogateescape"):
-        if b in b" \t\n\r\f\v":
+    for c in text:
+        if c in " \t\n\r\f\v" or (utf8 and ord(c) > 0x7F and ((c.isspace() and c not in "\x85\u2028\u2029") or c in "\xa0\u2007\u202f\u2060")):
             in_word = False
-        elif 0x20 < b < 0x7F and not in_word:
+        elif (0x20 < ord(c) < 0x7F or (utf8 and ord(c) > 0x7F and unicodedata.category(c) not in ("Cc", "Cs", "Cn"))) and not in_word:
             in_word = True
             count += 1
     return count
