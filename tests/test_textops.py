@@ -98,9 +98,9 @@ def test_sed_in_a_utf8_locale_does_not_match_a_stray_byte_with_a_dot():
 def test_wc_w_classifies_characters_as_the_locale_does():
     import random
     r = random.Random(2)
-    chars = ["é", "\udcff", "a", " ", "\xa0", " ", "​", "\x01", "日", "\t", "\x85", " ", "\x7f", "\udc80", "b", "\xad",
-             "", "\U0001F600", "　", " ", "\x1c", " ", "᠎"]
-    for _ in range(150):
+    chars = ["\u00e9", "\udcff", "a", " ", "\xa0", "\u2003", "\u200b", "\x01", "\u65e5", "\t", "\x85", "\u2028", "\x7f", "\udc80", "b",
+             "\xad", "\ue000", "\U0001F600", "\u3000", "\u1680", "\x1c", "\u2007", "\u180e", "\u2060", "\u2029", "\u205f"]
+    for _ in range(300):
         text = "".join(r.choice(chars) for _ in range(r.randint(0, 8))) + "\n"
         for env, utf8 in (({"LC_ALL": "C"}, False), ({"LANG": "C.UTF-8"}, True)):
             real = int(subprocess.run(["wc", "-w"], input=to_bytes(text), capture_output=True, env=dict(env, PATH="/usr/bin:/bin")).stdout)

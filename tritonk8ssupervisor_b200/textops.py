@@ -154,6 +154,10 @@ def wc_l(text: str) -> int:
     return text.count("\n")
 
 
+#: what separates words for GNU wc in a UTF-8 locale, beyond the ASCII blanks (found by asking it)
+_UTF8_BLANKS = frozenset("\xa0\u1680\u2000\u2001\u2002\u2003\u2004\u2005\u2006\u2007\u2008\u2009\u200a\u202f\u205f\u2060\u3000")
+
+
 def wc_w(text: str, utf8: bool = False) -> int:
     """``wc -w``: a word is a run of non-blank characters holding at least one printable
     one; what is neither (control characters, bytes that are no character) starts no word
@@ -161,9 +165,9 @@ def wc_w(text: str, utf8: bool = False) -> int:
     the characters beyond it are classified too."""
     count, in_word = 0, False
     for c in text:
-        if c in " \t\n\r\f\v" or (utf8 and ord(c) > 0x7F and ((c.isspace() and c not in "\x85\u2028\u2029") or c in "\xa0\u2007\u202f\u2060")):
+        if c in " \t\n\r\f\v" or (utf8 and ord(c) > 0x7F and c in _UTF8_BLANKS):
             in_word = False
-        elif (0x20 < ord(c) < 0x7F or (utf8 and ord(c) > 0x7F and unicodedata.category(c) not in ("Cc", "Cs", "Cn"))) and not in_word:
+        elif (0x20 < ord(c) < 0x7F or (utf8 and ord(c) > 0x7F and unicodedata.category(c) not in ("Cc", "Cs", "Cn", "Zl", "Zp"))) and not in_word:
             in_word = True
             count += 1
     return count
