@@ -93,3 +93,22 @@ def test_quoted_text_is_never_a_pattern(tmp_path):
     word = [(bashsem.quote_for_glob(str(tmp_path / "h*me") + "/"), False), ("id_*", True)]
     assert bashsem.expand_word(word, str(tmp_path)) == [str(tmp_path / "h*me" / "id_rsa")]
     assert os.path.exists(str(tmp_path / "home" / "id_rsa"))
+
+
+def test_utf8_locale_matches_bash(tmp_path):
+    """LANG=C.UTF-8: a multi-byte character is one character for ``?`` and for bracket
+    expressions; with a byte that is no character anywhere, bash falls back on bytes."""
+    r = random.Random(5)
+    pch = list("ab[]-!*?\\()|+@") + ["é", "日", "\udcff", "[:alpha:]", "[:upper:]", "[:punct:]", "[a-é]", "[é-日]",
+                                     "[!é]", "+(", "@(", "[:space:]", "[:print:]"]
+    sch = list("ab[-*?") + ["é", "日", "\udcff", "É", "\xa0", "¿", " "]
+    pairs = [("".join(r.choice(sch) for _ in range(r.randint(0, 4))), "".join(r.choice(pch) for _ in range(r.randint(0, 5))))
+             for _ in range(1200)]
+    pairs += [(s, s) for s, _ in pairs[:100]] + [("zéz", "z?z"), ("zéz", "z??z"), ("\udcffÉ", "[!é][!é]")]
+    script = ["t() { if [[ $1 == $2 ]]; then echo 1; else echo 0; fi; }"] + ["t %s %s" % (_q(s), _q(p)) for s, p in pairs]
+    path = tmp_path / "m8.sh"
+    path.write_text("\n".join(script) + "\n")
+    out = subprocess.run(["bash", str(path)], capture_output=True, env={"LANG": "C.UTF-8", "PATH": "/usr/bin:/bin"}, timeout=120).stdout.decode().split()
+    assert len(out) == len(pairs)
+    got = [shmatch.strmatch(p, s, shmatch.EXTMATCH | shmatch.UTF8) for s, p in pairs]
+    assert [(ascii(c), w, g) for c, w, g in zip(pairs, [o == "1" for o in out], got) if w != g] == []

@@ -149,13 +149,24 @@ def _has_glob_chars(word: str) -> bool:
     return False
 
 
-def pattern_match(s: str, pat: str) -> bool:
+def pattern_match(s: str, pat: str, utf8: bool = False) -> bool:
     """``[[ $s == $pat ]]`` with an unquoted right-hand side (setup.sh:351,394,443):
     a pattern match, with the extended operators bash switches on inside ``[[ ]]``."""
-    return shmatch.strmatch(pat, s, shmatch.EXTMATCH)
+    return shmatch.strmatch(pat, s, shmatch.EXTMATCH | (shmatch.UTF8 if utf8 else 0))
 
 
-def _glob_component(pattern: str) -> Callable[[str], bool]:
+class Cwd(str):
+    """A directory to expand pathnames in, which also knows whether the locale's character set is
+    UTF-8 (``?`` then matches a multi-byte character as one)."""
+    utf8 = False
+
+    def __new__(cls, path: str, utf8: bool = False):
+        obj = super().__new__(cls, path)
+        obj.utf8 = utf8
+        return obj
+
+
+def _glob_component(pattern: str, utf8: bool = False) -> Callable[[str], bool]:
     """Matcher for one pathname component (no extended operators: extglob is off in a script)."""
     # quoted text (see quote_for_glob) reaches the matcher as backslash-escaped characters
     pattern = "".join("\\" + _unquote(c) if _unquote(c) != c else c for c in pattern)
@@ -163,7 +174,7 @@ def _glob_component(pattern: str) -> Callable[[str], bool]:
     def match(name: str) -> bool:
         if name in (".", ".."):
             return False  # globskipdots (default on in bash 5.2)
-        return shmatch.strmatch(pattern, name, shmatch.PERIOD)
+        return shmatch.strmatch(pattern, name, shmatch.PERIOD | (shmatch.UTF8 if utf8 else 0))
     return match
 
 
@@ -194,7 +205,7 @@ def glob_word(word: str, cwd: str) -> List[str]:
             cands = nxt
             continue
         if _has_glob_chars(comp):
-            m = _glob_component(comp)
+            m = _glob_component(comp, getattr(cwd, "utf8", False))
             for disp, fs in cands:
                 try:
                     names = os.listdir(fs)

@@ -443,6 +443,12 @@ EDGE += [
              keygen_sha={},
              note="sed 's/.pub$//' in a UTF-8 locale: the dot does not match a byte that is no character, so 'k<ff>pub' keeps "
                   "its name (in the C locale it would be asked about as 'k')"),
+    Scenario(name="env_utf8_question_mark_is_a_character", stdin=_answers("?", "??", "", "", "", "", "", "", "yes"),
+             env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"], pre_files={"\u00e9": "", "\u65e5": ""},
+             note="pathname expansion of an answer in a UTF-8 locale: `?` matches the files called é and 日 (one character "
+                  "each), `??` neither; in the C locale it is the other way round for é (two bytes)"),
+    Scenario(name="text_question_marks_in_the_c_locale", stdin=_answers("?", "??", "", "", "", "", "", "", "yes"),
+             pre_files={"\u00e9": "", "\u65e5": ""}, note="... as here: `??` is é, `?` is nothing"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

@@ -21,6 +21,7 @@ from typing import Optional
 PATHNAME = 1        # a slash is matched only by a slash
 PERIOD = 2          # a leading period is matched only by a period
 EXTMATCH = 4        # ?(..) *(..) +(..) @(..) !(..)
+UTF8 = 8            # the locale's character set is UTF-8: a multi-byte character is one character
 
 _CLASSES = {
     "alnum": lambda c: c.isascii() and c.isalnum(), "alpha": lambda c: c.isascii() and c.isalpha(),
@@ -41,6 +42,17 @@ _COLLSYMS = {"NUL": "\0", "tab": "\t", "newline": "\n", "space": " ", "hyphen": 
              "grave-accent": "`", "left-brace": "{", "left-curly-bracket": "{", "right-brace": "}", "right-curly-bracket": "}",
              "zero": "0", "one": "1", "two": "2", "three": "3", "four": "4", "five": "5", "six": "6", "seven": "7", "eight": "8",
              "nine": "9"}
+
+
+def _wide_class(name: str, c: str) -> bool:
+    """Character classes beyond ASCII, as a UTF-8 locale has them (a byte that is no character belongs to none)."""
+    if "\udc80" <= c <= "\udcff":
+        return False
+    import unicodedata
+    cat = unicodedata.category(c)
+    return {"alnum": c.isalnum(), "alpha": c.isalpha(), "ascii": False, "blank": cat == "Zs", "cntrl": cat == "Cc",
+            "digit": False, "graph": cat[0] not in "CZ", "lower": c.islower(), "print": cat[0] != "C" and cat not in ("Zl", "Zp"),
+            "punct": cat[0] in "PS", "space": c.isspace(), "upper": c.isupper(), "word": c.isalnum(), "xdigit": False}[name]
 
 
 def _at(text: str, i: int) -> str:
@@ -93,7 +105,7 @@ def _bracket(pat: str, p: int, test: str, flags: int) -> Optional[int]:
             close = pat.find(":]", p + 1)
             if close != -1:
                 name = pat[p + 1:close]
-                ok = name in _CLASSES and _CLASSES[name](test)
+                ok = name in _CLASSES and (_wide_class(name, test) if (flags & UTF8) and ord(test) > 127 else _CLASSES[name](test))
                 p = close + 2
                 if ok:
                     p += 1
@@ -398,7 +410,11 @@ def _bytes(text: str) -> str:
 
 def strmatch(pattern: str, text: str, flags: int = 0) -> bool:
     """Does ``text`` match ``pattern``?  (bash ``strmatch``; C locale, i.e. byte by
-    byte: a two-byte character is matched by ``??``, not by ``?``)"""
-    pattern, text = _bytes(pattern), _bytes(text)
+    byte: a two-byte character is matched by ``??``, not by ``?``; with the ``UTF8`` flag,
+    character by character, a byte that is no character counting as one)"""
+    if (flags & UTF8) and any("\udc80" <= c <= "\udcff" for c in pattern + text):
+        flags &= ~UTF8          # bash cannot convert either to wide characters and falls back on bytes
+    if not flags & UTF8:
+        pattern, text = _bytes(pattern), _bytes(text)
     m = _Matcher(pattern, text)
     return m.gmatch(0, len(text), 0, len(pattern), flags)

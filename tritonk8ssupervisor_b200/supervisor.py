@@ -93,11 +93,13 @@ class Supervisor:
         # reference's children see
         for knob in OWN_ENV:
             rt.env.pop(knob, None)
+        #: the character set of the locale is UTF-8: grep then takes bytes that are not valid UTF-8 for binary data
+        self.utf8 = rt.utf8_locale()
+        #: where unquoted words are pathname-expanded (the workspace), with the locale's idea of a character
+        self.root = sh.Cwd(rt.root, self.utf8)
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
         self._shell_bookkeeping()
-        #: the character set of the locale is UTF-8: grep then takes bytes that are not valid UTF-8 for binary data
-        self.utf8 = rt.utf8_locale()
         self._tables: Dict[tuple, str] = {}
         self._lineno = 0
         self._scopes: List[Dict[str, tuple]] = []
@@ -120,7 +122,7 @@ class Supervisor:
             self.rt.err("bash: warning: shell level (%d) too high, resetting to 1\n" % level)
             level = 1
         self.export("SHLVL", str(level))
-        root = os.path.abspath(self.rt.root)
+        root = os.path.abspath(self.root)
         pwd = env.get("PWD", "")
         try:
             inherited_ok = pwd.startswith("/") and os.path.samefile(pwd, root)
@@ -230,15 +232,15 @@ class Supervisor:
 
     def echo_var(self, value: str) -> str:
         """``$(echo $VALUE)``: unquoted, so field-split and globbed in the workspace."""
-        return sh.cmdsubst(sh.echo_unquoted(value, self.rt.root))
+        return sh.cmdsubst(sh.echo_unquoted(value, self.root))
 
     def unq(self, value: str) -> str:
         """``$(echo $VALUE | sed 's/"//g')`` -- the reference's quote-stripper."""
-        return sh.cmdsubst(tx.strip_dquotes(sh.echo_unquoted(value, self.rt.root)))
+        return sh.cmdsubst(tx.strip_dquotes(sh.echo_unquoted(value, self.root)))
 
     def args_of(self, value: str) -> List[str]:
         """Positional parameters produced by an unquoted ``$VALUE`` argument."""
-        return sh.expand_unquoted(value, self.rt.root)
+        return sh.expand_unquoted(value, self.root)
 
     def append_line(self, rel: str, line: str, lineno: int = 0) -> None:
         """``echo "<line>" >> rel``; a failing redirection ends the script (errexit).
@@ -455,10 +457,10 @@ class Supervisor:
         found = False
         for f in self.args_of(self._ls_ssh_dir()):
             # ~/.ssh/$(echo $f | sed 's/.pub$//') -- unquoted, so it can be several words
-            stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, rt.root), r".pub$", "", utf8=self.utf8))
+            stem = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(f, self.root), r".pub$", "", utf8=self.utf8))
             v["f"] = f                                 # the loop variable is a global of the script
             # tilde expansion yields quoted text: never split, never globbed
-            key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], rt.root)
+            key_args = sh.expand_word([(sh.quote_for_glob(self.tilde("~/.ssh/")), False), (stem, True)], self.root)
             _, out = rt.run(["ssh-keygen", "-E", "md5", "-lf"] + key_args, stdout=CAPTURE, stderr=DEVNULL)
             fp = self.subst(tx.sed_sub(tx.awk_print_field(out, 2), r"^MD5:", ""), 217)
             matched_at = 218
@@ -505,7 +507,7 @@ class Supervisor:
         Both branches ``echo`` unquoted.  ``lineno`` is the reference line of the
         call, which bash names when it drops a NUL byte from the substitution."""
         answer, _ok = self.rt.read("%s (%s) " % (message, default))
-        printed = sh.echo_unquoted(default if answer == "" else answer, self.rt.root)
+        printed = sh.echo_unquoted(default if answer == "" else answer, self.root)
         if "\x00" in printed:
             self.rt.err("%s: line %d: warning: command substitution: ignored null byte in input\n" % (self.program, lineno))
         return sh.cmdsubst(printed)
@@ -543,7 +545,7 @@ class Supervisor:
             self.v[loop_var] = row
             count += 1
             self.v["tmp"] = str(count)
-            shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.rt.root), r"=", "  ", count=0))
+            shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.root), r"=", "  ", count=0))
             self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]), {"network": 316, "package": 409}.get(loop_var, 0))
             if default_prefix is not None and row.startswith(default_prefix):
                 default_at = count
@@ -635,7 +637,7 @@ class Supervisor:
     def _normalise_list(self, value: str) -> str:
         """``echo $V | tr ',' '\\n' | sort | uniq | tr '\\n' ',' | sed 's/\\(.*\\),$/\\1/'``
         -- lexical sort: ``10,2`` stays ``10,2`` (setup.sh:333-334)."""
-        t = tx.uniq(tx.sort_lines(tx.tr(sh.echo_unquoted(value, self.rt.root), ",", "\n")))
+        t = tx.uniq(tx.sort_lines(tx.tr(sh.echo_unquoted(value, self.root), ",", "\n")))
         return sh.cmdsubst(tx.sed_sub(tx.tr(t, "\n", ","), r"(.*),$", r"\1", utf8=self.utf8))
 
     def _out_of_range(self, items: List[str], count: int, var: str, lineno: int) -> int:
@@ -665,7 +667,7 @@ class Supervisor:
             answer = self.get_argument(message, self.unq(v[var]), lineno)
             v[var] = self._normalise_list(v[var])
             answer = v["tmp_" + var] = self._normalise_list(answer)
-            shown = sh.echo_unquoted(answer, self.rt.root)
+            shown = sh.echo_unquoted(answer, self.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_LIST_RE)) != "":
                 v["gotValidInput"] = "true"
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
@@ -678,7 +680,7 @@ class Supervisor:
                 if bad == 0:
                     v[var] = self.network_ids(self.args_of(answer))
                     return
-            elif sh.pattern_match(answer, v[var]):
+            elif sh.pattern_match(answer, v[var], self.utf8):
                 v["gotValidInput"] = "true"
                 return  # the default UUID list was left as it is
             else:
@@ -693,7 +695,7 @@ class Supervisor:
         while True:
             answer = v["tmp_HOST_PACKAGE"] = self.get_argument("What KVM package should the master and nodes run on:",
                                                                self.unq(v["HOST_PACKAGE"]), 425)
-            shown = sh.echo_unquoted(answer, self.rt.root)
+            shown = sh.echo_unquoted(answer, self.root)
             if sh.cmdsubst(tx.grep(shown, INDEX_RE)) != "":
                 v["gotValidInput"] = "true"
                 items = self.args_of(sh.cmdsubst(tx.tr(shown, ",", "\n")))
@@ -707,7 +709,7 @@ class Supervisor:
                     v["HOST_PACKAGE"] = self.package_id(self.args_of(answer))
                     self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]), lineno=440)
                     return
-            elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"])):
+            elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"]), self.utf8):
                 v["gotValidInput"] = "true"
                 return
             else:
@@ -723,7 +725,7 @@ class Supervisor:
         (setup.sh:257 vs :536), which is the ordering hazard of SURVEY.md §7.4."""
         arg1 = args[0] if args else ""
         with self.scope():                            # runs inside $(...): its assignments do not outlive it
-            values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.rt.root), ",", " "))
+            values = sh.cmdsubst(tx.tr(sh.echo_unquoted(arg1, self.root), ",", " "))
             self.subshell_set("values", values)
             self.local("networks")
             acc = ""
@@ -897,7 +899,7 @@ class Supervisor:
         rel = "terraform/rancher.tf"
         if kind in ("master", "host"):
             nets = v.get("RANCHER_MASTER_NETWORKS" if kind == "master" else "KUBERNETES_NODE_NETWORKS", "")
-            net_list = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(nets, self.rt.root), r",", '","', count=0))
+            net_list = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(nets, self.root), r",", '","', count=0))
             block = [
                 "",
                 'module "%s" {' % label,
@@ -1060,7 +1062,7 @@ class Supervisor:
         return sh.expand_word([
             ("http://", False), (self.cat_subst("terraform/masters.ip", line), True),
             (":8080/r/projects/", False), (self.cat_subst("ansible/tmp/kubernetes_environment.id", line), True),
-            ("/kubernetes-dashboard:9090/", False)], self.rt.root)
+            ("/kubernetes-dashboard:9090/", False)], self.root)
 
     def _curl_dashboard(self, line: int) -> Tuple[int, str]:
         # cRetVal=$(curl ...) at :66 holds curl alone; at :74 curl heads a pipeline
@@ -1094,7 +1096,7 @@ class Supervisor:
             status, body = self._curl_dashboard(66)
             self.must(status)  # cRetVal=$(curl …): a failing curl ends the script
             v["cRetVal"] = self.subst(body, 66)
-            shown = sh.echo_unquoted(v["cRetVal"], rt.root)
+            shown = sh.echo_unquoted(v["cRetVal"], self.root)
             if tx.wc_l(tx.grep(shown, r"kubernetes", ignore_case=True, binary=self._binary_matches, utf8=self.utf8)) != 0:
                 up = True
                 v["KUBERNETES_DASHBOARD_UP"] = "true"
@@ -1172,13 +1174,13 @@ class Supervisor:
         for rel in ("terraform/hosts.ip", "terraform/masters.ip", "terraform/rancher.tf"):
             _rm_rf(rt.path(rel))
         for pattern in ("terraform/terraform.*", "terraform/.terraform*"):
-            for rel in sh.glob_word(pattern, rt.root):
+            for rel in sh.glob_word(pattern, self.root):
                 _rm_rf(rt.path(rel))
         self._rewrite_private_key_file("ansible/ansible.cfg", "tmp", "~", "", shown_src="ansible/ansible.cfg", lineno=511)
         # rm -f ansible/hosts ansible/*retry ansible/ansible.cfg.tmp 2>&1 >> /dev/null: rm goes through
         # all its arguments, complains on the script's *stdout* (2>&1 comes first) and fails at the end
         failed = False
-        for rel in ["ansible/hosts"] + sh.glob_word("ansible/*retry", rt.root) + ["ansible/ansible.cfg.tmp"]:
+        for rel in ["ansible/hosts"] + sh.glob_word("ansible/*retry", self.root) + ["ansible/ansible.cfg.tmp"]:
             p = rt.path(rel)
             if os.path.isdir(p) and not os.path.islink(p):
                 try:
@@ -1191,7 +1193,7 @@ class Supervisor:
         if failed:
             raise ScriptExit(1)
         _rm_rf(rt.path("config"))
-        for rel in sh.glob_word("tmp/*", rt.root):
+        for rel in sh.glob_word("tmp/*", self.root):
             _rm_rf(rt.path(rel))
 
 
