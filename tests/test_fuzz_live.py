@@ -281,3 +281,15 @@ def make_binary(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(3))
 def test_property_fuzzed_binary_output(ref_root, block):
     assert _sweep(ref_root, make_binary, range(15 * block, 15 * (block + 1))) == []
+
+
+# --- the same scenarios in a UTF-8 locale (grep, sed and bash's matcher all look at characters then) ---
+def make_utf8(seed: int) -> Scenario:
+    import dataclasses
+    sc = (make, make_wide, make_binary)[seed % 3](seed)
+    return dataclasses.replace(sc, env=dict(sc.env, LANG="C.UTF-8"), unset_env=["LC_ALL"])
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_in_a_utf8_locale(ref_root, block):
+    assert _sweep(ref_root, make_utf8, range(500 + 15 * block, 500 + 15 * (block + 1))) == []
