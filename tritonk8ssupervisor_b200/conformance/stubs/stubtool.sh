@@ -30,10 +30,10 @@ printf '%s|%s|%s\n' "$tool" "$rel" "$*" >> "$S/calls.log"
 # of it.  Left out: this stub's own plumbing, and PYTHON* (how the test harness
 # makes an uninstalled Python package importable).
 sbx=${S%/state}
-envdump() { env | LC_ALL=C grep -a -v -E '^(TK8S_STUB_|PYTHON)' | LC_ALL=C sort | LC_ALL=C sed "s|$sbx|<SBX>|g"; }
+envdump() { env | LC_ALL=C sort | LC_ALL=C sed -e '/^TK8S_STUB_/d' -e '/^PYTHON/d' -e "s|$sbx|<SBX>|g"; }
 case "$tool" in
     terraform|ansible-playbook) envdump | sed 's/^/  env:/' >> "$S/calls.log" ;;
-    *) printf '  env~:%s\n' "$(envdump | md5sum | cut -c1-12)" >> "$S/calls.log" ;;
+    *) sum=$(envdump | md5sum); printf '  env~:%.12s\n' "$sum" >> "$S/calls.log" ;;
 esac
 
 # modelled latency (milliseconds) of a tool that sits on a network round trip:
