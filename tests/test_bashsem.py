@@ -143,3 +143,19 @@ def test_cmdsubst():
     assert bashsem.cmdsubst("a\n\n") == "a"
     assert bashsem.cmdsubst("a\nb\n") == "a\nb"
     assert bashsem.cmdsubst("\n") == ""
+
+
+def test_echo_e_escapes_in_both_locales():
+    """\\uHHHH / \\UHHHHHHHH are written in the locale's character set: UTF-8 where that is
+    the locale's, otherwise only ASCII can be and the rest comes back as the escape it was."""
+    import random
+    import subprocess
+    from tritonk8ssupervisor_b200 import bashsem as sh
+    r = random.Random(3)
+    tokens = ["\\u", "\\U", "\\x", "\\0", "\\", "\\\\", "4", "1", "e", "9", "F", "0", "Z", " ", "a", "\\n", "\\c", "\\t", "8", "d", "D8", "00"]
+    cases = ["\\u00e9", "\\u65e5x", "\\U0001F600", "\\u41", "\\uZZ", "\\u", "\\ud800", "\\U00110000", "\\U7FFFFFFF", "\\UFFFFFFFF",
+             "\\U00e9\\u7f\\u80"] + ["".join(r.choice(tokens) for _ in range(r.randint(1, 8))) for _ in range(150)]
+    for env, utf8 in (({"LC_ALL": "C"}, False), ({"LANG": "C.UTF-8"}, True)):
+        for text in cases:
+            real = subprocess.run(["bash", "-c", 'echo -e "$1"', "_", text], capture_output=True, env=dict(env, PATH="/usr/bin:/bin")).stdout
+            assert sh.to_bytes(sh.echo_builtin(["-e", text], utf8)) == real, (text, utf8)

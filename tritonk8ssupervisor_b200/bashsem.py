@@ -293,9 +293,34 @@ def expand_word(segments: Sequence[Tuple[str, bool]], cwd: str) -> List[str]:
 _ECHO_OPT = re.compile(r"-[neE]+\Z")
 
 
-def _echo_escapes(s: str) -> Tuple[str, bool]:
+def _encode_wide(value: int) -> str:
+    """UTF-8 as bash writes it for any 31-bit value (surrogates and what lies beyond U+10FFFF included)."""
+    if value < 0x80:
+        return chr(value)
+    if value < 0x800:
+        raw = [0xC0 | value >> 6]
+        rest = 1
+    elif value < 0x10000:
+        raw = [0xE0 | value >> 12]
+        rest = 2
+    elif value < 0x200000:
+        raw = [0xF0 | value >> 18]
+        rest = 3
+    elif value < 0x4000000:
+        raw = [0xF8 | value >> 24]
+        rest = 4
+    else:
+        raw = [0xFC | value >> 30]
+        rest = 5
+    raw += [0x80 | (value >> (6 * k)) & 0x3F for k in range(rest - 1, -1, -1)]
+    return from_bytes(bytes(raw))
+
+
+def _echo_escapes(s: str, utf8: bool = False) -> Tuple[str, bool]:
     """Backslash processing of ``echo -e``; returns (text, stop) where stop is
-    True after ``\\c``."""
+    True after ``\\c``.  ``\\uHHHH`` / ``\\UHHHHHHHH`` come out in the locale's
+    character set: UTF-8 when it is that (``utf8``); in the C locale only ASCII
+    can, anything else is written back as the escape it was."""
     out: List[str] = []
     i, n = 0, len(s)
     simple = {"a": "\a", "b": "\b", "e": "\x1b", "E": "\x1b", "f": "\f", "n": "\n",
@@ -330,12 +355,30 @@ def _echo_escapes(s: str) -> Tuple[str, bool]:
             else:
                 out.append(from_bytes(bytes([int(s[i:j], 16) & 0xFF])))
                 i = j
+        elif d in "uU":
+            width = 4 if d == "u" else 8
+            j = i
+            while j < n and j - i < width and s[j] in "0123456789abcdefABCDEF":
+                j += 1
+            if j == i:
+                out.append("\\" + d)
+            else:
+                value = int(s[i:j], 16)
+                if value < 0x80:
+                    out.append(chr(value))
+                elif value > 0x7FFFFFFF:
+                    pass                                   # not a code point bash can convert: nothing is written
+                elif utf8:
+                    out.append(_encode_wide(value))
+                else:
+                    out.append(("\\u%04X" if value <= 0xFFFF else "\\U%08X") % value)
+                i = j
         else:
             out.append("\\" + d)
     return "".join(out), False
 
 
-def echo_builtin(args: Sequence[str]) -> str:
+def echo_builtin(args: Sequence[str], utf8: bool = False) -> str:
     """Exactly what ``echo ARGS...`` writes (including the trailing newline,
     or not)."""
     newline, escapes = True, False
@@ -351,7 +394,7 @@ def echo_builtin(args: Sequence[str]) -> str:
         k += 1
     text = " ".join(args[k:])
     if escapes:
-        text, stop = _echo_escapes(text)
+        text, stop = _echo_escapes(text, utf8)
         if stop:
             return text
     return text + ("\n" if newline else "")
@@ -365,4 +408,4 @@ def cmdsubst(output: str) -> str:
 def echo_unquoted(value: str, cwd: str) -> str:
     """``echo $value`` -- the workhorse of the reference (unquoted on purpose
     there or not, it is what decides the bytes)."""
-    return echo_builtin(expand_unquoted(value, cwd))
+    return echo_builtin(expand_unquoted(value, cwd), getattr(cwd, "utf8", False))

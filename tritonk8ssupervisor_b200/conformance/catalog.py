@@ -449,6 +449,14 @@ EDGE += [
                   "each), `??` neither; in the C locale it is the other way round for é (two bytes)"),
     Scenario(name="text_question_marks_in_the_c_locale", stdin=_answers("?", "??", "", "", "", "", "", "", "yes"),
              pre_files={"\u00e9": "", "\u65e5": ""}, note="... as here: `??` is é, `?` is nothing"),
+    Scenario(name="env_utf8_unicode_escapes", stdin=_answers("-e caf\\\\u00e9 \\\\U0001F600", "-e \\\\ud800 \\\\u41", "", "", "", "", "", "", "yes"),
+             env={"LANG": "C.UTF-8"}, unset_env=["LC_ALL"],
+             networks=triton_table([("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4"), ("caf\\u00e9", "0b206464-d655-4723-a848-86d0f28764c8")]),
+             note="echo -e writes \\uHHHH in the locale's character set: UTF-8 here -- in the answers and in the menu, "
+                  "whose rows go through echo -e as well"),
+    Scenario(name="text_unicode_escapes_in_the_c_locale", stdin=_answers("-e caf\\\\u00e9 \\\\U0001F600", "-e \\\\ud800 \\\\u41", "", "", "", "", "", "", "yes"),
+             networks=triton_table([("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4"), ("caf\\u00e9", "0b206464-d655-4723-a848-86d0f28764c8")]),
+             note="... in the C locale only ASCII can be written: \\u00e9 comes back as \\u00E9, \\u41 is A"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

@@ -546,7 +546,7 @@ class Supervisor:
             count += 1
             self.v["tmp"] = str(count)
             shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.root), r"=", "  ", count=0))
-            self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)]), {"network": 316, "package": 409}.get(loop_var, 0))
+            self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)], self.utf8), {"network": 316, "package": 409}.get(loop_var, 0))
             if default_prefix is not None and row.startswith(default_prefix):
                 default_at = count
         return count, default_at
