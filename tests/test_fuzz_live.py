@@ -293,3 +293,33 @@ def make_utf8(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(2))
 def test_property_fuzzed_in_a_utf8_locale(ref_root, block):
     assert _sweep(ref_root, make_utf8, range(500 + 12 * block, 500 + 12 * (block + 1))) == []
+
+
+# --- answers and table names full of echo's escapes, in both locales -----------------------------------
+_ESC = ["-e ", "-e ", "-E ", "-ne ", "-en ", "-eE ", "-n ", "- ", "-ex ", "\\\\u00e9", "\\\\u65e5", "\\\\U0001F600", "\\\\u41", "\\\\ud800", "\\\\u",
+        "\\\\x41", "\\\\xe9", "\\\\xc3\\\\xa9", "\\\\0101", "\\\\0351", "\\\\101", "\\\\c", "\\\\e", "\\\\E", "\\\\a", "\\\\b", "\\\\f", "\\\\v", "\\\\r",
+        "\\\\n", "\\\\t", "\\\\\\\\", "\\\\", "\\", "a", "1", " ", "é", "\udcff", "x", "2", ","]
+_ESC_NAMES = ["caf\\u00e9", "a\\x41b", "t\\tb", "n\\nl", "c\\cz", "o\\0101", "b\\\\s", "e\\e[1m", "u\\U0001F600", "bad\\xzz", "\\u41-kvm-x",
+              "k\\u00e9-kvm-1"]
+
+
+def make_escapes(seed: int) -> Scenario:
+    import dataclasses
+    sc = make(seed)
+    r = random.Random(seed * 31 + 7)
+    lines = ["".join(r.choice(_ESC) for _ in range(r.randint(1, 6))) if r.random() < 0.6 else r.choice(["", "1", "2", "1,2", "3"])
+             for _ in range(r.randint(3, 14))]
+    kw = {"stdin": "\n".join(lines) + "\n" + r.choice(["yes\n", "", "yes"])}
+    if r.random() < 0.5:
+        kw["networks"] = triton_table(list(DOC_NETWORKS)[:2] + [(r.choice(_ESC_NAMES), "id-%d" % i) for i in range(r.randint(1, 3))])
+    if r.random() < 0.5:
+        kw["packages"] = triton_table(list(DOC_PACKAGES)[:2] + [(r.choice(_ESC_NAMES) + "-kvm-", "pid-%d" % i) for i in range(r.randint(1, 3))])
+    if seed % 2:
+        kw["env"] = dict(sc.env, LANG="C.UTF-8")
+        kw["unset_env"] = ["LC_ALL"]
+    return dataclasses.replace(sc, **kw)
+
+
+@pytest.mark.parametrize("block", range(2))
+def test_property_fuzzed_echo_escapes(ref_root, block):
+    assert _sweep(ref_root, make_escapes, range(12 * block, 12 * (block + 1))) == []
