@@ -323,3 +323,36 @@ def make_escapes(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(2))
 def test_property_fuzzed_echo_escapes(ref_root, block):
     assert _sweep(ref_root, make_escapes, range(12 * block, 12 * (block + 1))) == []
+
+
+# --- answers that leave a word echo (and then sed) takes for options in the variable --------------------
+_OPTS = ["e", "n", "E", "ne", "en", "eE", "nE", "Ee", "nn", "neE", "Ene", "x", "", "-", "ex", "e "]      # not "ee": refused (sed would execute)
+_OPT_WORDS = ["1", "2", "3", "14", "1,2", "2,1,2", "1.5", "/b/", "$", "x", "08", "i", "0", "99", "19", "-1", "1 2", "*", "a b", "", "tmp",
+              "kube", "-e", "-n"]
+_OPT_SEP = [" ", "\\\\\\\\n", "\\\\\\\\t", ",", "\\\\\\\\c", "\\\\n"]
+
+
+def make_option_words(seed: int) -> Scenario:
+    import dataclasses
+    sc = make(seed)
+    r = random.Random(seed * 17 + 3)
+
+    def answer():
+        k = r.random()
+        if k < 0.25:
+            return r.choice(["", "", "1", "2", "1,2", "km"])
+        words = [r.choice(_OPT_WORDS) for _ in range(r.randint(1, 3))]
+        payload = words[0] + "".join(r.choice(_OPT_SEP) + w for w in words[1:])
+        if k < 0.85:
+            return "-e \\\\055" + r.choice(_OPTS) + " " + payload           # read and the first echo leave "-<opts> <payload>"
+        return r.choice(["-e ", "-n ", "-E ", "-ne ", ""]) + payload
+    kw = {"stdin": "\n".join(answer() for _ in range(r.randint(6, 14))) + "\n" + r.choice(["yes\n", "", "yes", "yes\nyes\n"])}
+    if seed % 3 == 0:
+        kw["env"] = dict(sc.env, LANG="C.UTF-8")
+        kw["unset_env"] = ["LC_ALL"]
+    return dataclasses.replace(sc, **kw)
+
+
+@pytest.mark.parametrize("block", range(2))
+def test_property_fuzzed_option_words(ref_root, block):
+    assert _sweep(ref_root, make_option_words, range(12 * block, 12 * (block + 1))) == []

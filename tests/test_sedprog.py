@@ -89,3 +89,17 @@ def test_unrestated_program_is_refused_end_to_end():
     assert obs.exit_status == 2
     assert "refusing to go on: the key path spliced into the sed program at line 133" in obs.stderr
     assert "ansible/ansible.cfg" not in obs.files          # untouched
+
+
+def test_index_word_that_makes_sed_execute_is_refused():
+    """An answer that leaves ``-ee 1`` in the variable: `sed -n "-ee"p` is `sed -n -e ep`, and GNU sed's `e`
+    command runs ``p`` through sh once per row.  Status 2, no terraform input generated."""
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    from tritonk8ssupervisor_b200.conformance.harness import WORKSPACE_TEMPLATE
+    from tritonk8ssupervisor_b200.conformance.sandbox import run_in_sandbox
+    from tritonk8ssupervisor_b200.conformance.scenario import Scenario
+    sc = Scenario(name="sedexec", stdin="\n" * 7 + "-e \\\\055ee 1\n\nyes\n")
+    obs = run_in_sandbox(rp.REPLACEMENT_ARGV, WORKSPACE_TEMPLATE, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert obs.exit_status == 2
+    assert "refusing to go on: the index spliced into the sed program at line 541 makes it 'ep'" in obs.stderr
+    assert "terraform/rancher.tf" not in obs.files and not [c for c in obs.calls if c.startswith("terraform")]

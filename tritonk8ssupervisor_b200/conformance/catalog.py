@@ -116,6 +116,15 @@ EDGE: List[Scenario] = [
              stdin=_answers("", "", "", "", "", "", "", "", "[a-", "1", "yes"),
              note="a '[' that finds no ']' is an ordinary character -- unless the search runs into a dangling range: '[a-' "
                   "matches nothing, not even itself, so the empty answer (= the default) is rejected until an index is typed"),
+    Scenario(name="pkg_index_word_is_sed_options_ne", stdin=_answers("", "", "", "", "", "", "", "-e \\\\055ne 1", "", "yes"),
+             note="the answer leaves '-ne 1' in the variable: echo takes -ne for its own options (the check sees '1'), and "
+                  "`sed -n \"-ne\"p` is `sed -n -n -e p`: every row is printed and HOST_PACKAGE is all 18 ids (setup.sh:427,541)"),
+    Scenario(name="pkg_index_word_is_sed_options_n", stdin=_answers("", "", "", "", "", "", "", "-e \\\\055n 1", "", "yes"),
+             note="... '-n': `sed -n -np` -- invalid option 'p', sed's usage on stderr, an empty package id"),
+    Scenario(name="pkg_index_word_is_sed_options_en", stdin=_answers("", "", "", "", "", "", "", "-e \\\\055en 1", "", "yes"),
+             note="... '-en': the script is 'np' -- extra characters after command"),
+    Scenario(name="pkg_index_word_is_sed_options_eE", stdin=_answers("", "", "", "", "", "", "", "-e \\\\055eE 1", "", "yes"),
+             note="... '-eE': the script is 'Ep' -- unknown command: `E'"),
     Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
              stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
     Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),

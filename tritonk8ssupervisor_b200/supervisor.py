@@ -733,7 +733,7 @@ class Supervisor:
                 self.subshell_set("network", index)   # what `triton` finds in its environment if `network` is exported
                 text = self._triton_table(TRITON_NETWORKS, 536)
                 rows = tx.grep(tx.sort_lines(text), r"^NAME *ID$", invert=True, binary=self._binary_matches, utf8=self.utf8)
-                acc = acc + "," + self.subst(tx.awk_last_field_if_many(self._nth_row(rows, index)), 536)
+                acc = acc + "," + self.subst(tx.awk_last_field_if_many(self._nth_row(rows, index, 536)), 536)
                 self.v["networks"] = acc
         t = tx.sed_sub(sh.echo_builtin([acc]), r"^,(.*)$", r"\1", utf8=self.utf8)
         return sh.cmdsubst(tx.sed_sub(t, r"(.*),$", r"\1", utf8=self.utf8))
@@ -746,18 +746,42 @@ class Supervisor:
         picked = self.subst(tx.awk_last_field_if_many(self._nth_row(rows, arg1)), 541)
         return sh.cmdsubst(sh.echo_builtin([picked]))
 
-    def _nth_row(self, rows: str, index: str) -> str:
-        """``sed -n "${index}p"``."""
-        if index.startswith("-e"):
-            # the word is then an option: -e with the script "<rest>p"
-            index = index[2:]
-        if not re.fullmatch(r"[0-9]+", index):
-            if index == "":
-                # `sed -n p` prints every row
-                return rows
-            self.rt.err("sed: -e expression #1, char %d: unknown command\n" % len(index))
+    def _nth_row(self, rows: str, index: str, lineno: int = 541) -> str:
+        """``sed -n "${index}p"``.  The index has been through the script's own check, which lets through numbers
+        and -- an answer such as ``-e \\055ne 1`` leaves ``-ne 1`` behind -- words `echo` takes for options:
+        `sed -n "-ne"p` is `sed -n -n -e p`."""
+        script = index + "p"
+        if len(index) > 1 and index.startswith("-"):
+            script = None
+            for k, flag in enumerate(index[1:], 1):
+                if flag in "nE":
+                    continue                          # -n again; -E: extended regular expressions, of which there are none
+                if flag == "e":
+                    script = index[k + 1:] + "p"      # the rest of the word is the script
+                    break
+                self._refuse_sed(script=index + "p", lineno=lineno)
+            if script is None:
+                self.rt.err("sed: invalid option -- 'p'\n" + tx.SED_USAGE)
+                return ""
+        if script == "p":
+            return rows                               # `sed -n p` prints every row
+        m = re.fullmatch(r"([0-9]+)p", script)
+        if m:
+            return tx.sed_print_line(rows, int(m.group(1)) & 0xFFFFFFFFFFFFFFFF)  # GNU sed line numbers wrap at 2**64
+        head = script.lstrip("0123456789")
+        at = len(script) - len(head) + 1
+        if head[0] == "n":                            # `n` wants `;`, a newline or the end after it
+            self.rt.err("sed: -e expression #1, char %d: extra characters after command\n" % (at + 1))
             return ""
-        return tx.sed_print_line(rows, int(index) & 0xFFFFFFFFFFFFFFFF)  # GNU sed line numbers wrap at 2**64
+        if head[0] not in "{}=abcdDeFgGhHilnNpPqQrRstTvwWxyz:#/\\$!~,+; \t\n":
+            self.rt.err("sed: -e expression #1, char %d: unknown command: `%s'\n" % (at, head[0]))
+            return ""
+        self._refuse_sed(script, lineno)
+
+    def _refuse_sed(self, script: str, lineno: int):
+        self.rt.err("%s: refusing to go on: the index spliced into the sed program at line %d makes it %s, which is not restated here\n"
+                    % (self.program, lineno, repr(script)))
+        raise ScriptExit(2)
 
     # ------------------------------------------------------------------
     # a7  verifyConfig  (setup.sh:452-483)

@@ -107,6 +107,52 @@ def strip_dquotes(text: str) -> str:
     """``sed 's/"//g'`` -- the quote-stripper used at 15+ sites (e.g. setup.sh:130)."""
     return text.replace('"', "")
 
+#: what GNU sed 4.9 prints below "invalid option" (its usage(), status 1): reachable at setup.sh:541 with an index
+#: word such as ``-n`` -- `sed -n "-n"p` is `sed -n -np`
+SED_USAGE = (
+    'Usage: sed [OPTION]... {script-only-if-no-other-script} [input-file]...\n'
+    '\n'
+    '  -n, --quiet, --silent\n'
+    '                 suppress automatic printing of pattern space\n'
+    '      --debug\n'
+    '                 annotate program execution\n'
+    '  -e script, --expression=script\n'
+    '                 add the script to the commands to be executed\n'
+    '  -f script-file, --file=script-file\n'
+    '                 add the contents of script-file to the commands to be executed\n'
+    '  --follow-symlinks\n'
+    '                 follow symlinks when processing in place\n'
+    '  -i[SUFFIX], --in-place[=SUFFIX]\n'
+    '                 edit files in place (makes backup if SUFFIX supplied)\n'
+    '  -l N, --line-length=N\n'
+    "                 specify the desired line-wrap length for the `l' command\n"
+    '  --posix\n'
+    '                 disable all GNU extensions.\n'
+    '  -E, -r, --regexp-extended\n'
+    '                 use extended regular expressions in the script\n'
+    '                 (for portability use POSIX -E).\n'
+    '  -s, --separate\n'
+    '                 consider files as separate rather than as a single,\n'
+    '                 continuous long stream.\n'
+    '      --sandbox\n'
+    '                 operate in sandbox mode (disable e/r/w commands).\n'
+    '  -u, --unbuffered\n'
+    '                 load minimal amounts of data from the input files and flush\n'
+    '                 the output buffers more often\n'
+    '  -z, --null-data\n'
+    '                 separate lines by NUL characters\n'
+    '      --help     display this help and exit\n'
+    '      --version  output version information and exit\n'
+    '\n'
+    'If no -e, --expression, -f, or --file option is given, then the first\n'
+    'non-option argument is taken as the sed script to interpret.  All\n'
+    'remaining arguments are names of input files; if no input files are\n'
+    'specified, then the standard input is read.\n'
+    '\n'
+    'GNU sed home page: <https://www.gnu.org/software/sed/>.\n'
+    'General help using GNU software: <https://www.gnu.org/gethelp/>.\n'
+)
+
 
 def sed_print_line(text: str, n: int) -> str:
     """``sed -n "${n}p"`` (setup.sh:536,541)."""
