@@ -159,3 +159,19 @@ def test_echo_e_escapes_in_both_locales():
         for text in cases:
             real = subprocess.run(["bash", "-c", 'echo -e "$1"', "_", text], capture_output=True, env=dict(env, PATH="/usr/bin:/bin")).stdout
             assert sh.to_bytes(sh.echo_builtin(["-e", text], utf8)) == real, (text, utf8)
+
+
+def test_declare_value_in_both_locales():
+    """`export -p` prints "value" -- or $'...' once the value holds something the locale cannot print."""
+    import random
+    import subprocess
+    from tritonk8ssupervisor_b200 import bashsem as sh
+    r = random.Random(1)
+    chars = list("ab \"$`\\'!*") + ["\t", "\n", "\x01", "\x7f", "\x1b", "\r", "é", "日", "\udcff", "\udc80", "​", "", "͸",
+                                    " ", "\xa0", "\xad", "\U0001f600", "\U000e0001", "￾", "̀"]
+    for env, utf8 in (({"LC_ALL": "C"}, False), ({"LANG": "C.UTF-8"}, True)):
+        for _ in range(150):
+            v = "".join(r.choice(chars) for _ in range(r.randint(0, 6)))
+            out = subprocess.run(["bash", "-c", 'V=$1; export V; export -p | grep -a "^declare -x V="', "_", v], capture_output=True,
+                                 env=dict(env, PATH="/usr/bin:/bin")).stdout.decode("utf-8", "surrogateescape")
+            assert "declare -x V=" + sh.declare_value(v, utf8) == out.split("\n")[0], (ascii(v), utf8)

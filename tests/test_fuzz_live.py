@@ -356,3 +356,31 @@ def make_option_words(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(2))
 def test_property_fuzzed_option_words(ref_root, block):
     assert _sweep(ref_root, make_option_words, range(12 * block, 12 * (block + 1))) == []
+
+
+@pytest.mark.parametrize("word", ["-p", "-n X", "-f", "--", "-x", "-n", "-", "-fn", "--help", "--x", "-a", "master", "A B=2"])
+def test_config_line_that_export_takes_for_options(ref_root, word):
+    """A description of three lines leaves WORD as a line of ./config, and setup.sh:546 runs `export "WORD"`."""
+    for stdin in ("-e a\\\\n%s\n\n\n\n\n\n\n\n\nyes\n" % word, "\n-e a\\\\n%s\\\\nQ=\n\n\n\n\n\n\nyes\n" % word):
+        sc = Scenario(name="exportword", stdin=stdin)
+        theirs = run_reference(sc, ref_root)
+        mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+        assert theirs.diff(mine) == []
+
+
+@pytest.mark.parametrize("line,why", [("RANDOM=4", "bash computes by itself"), ("HOSTNAME", "bash computes by itself"),
+                                      ("IFS=,", "changes how bash reads the rest of the script"),
+                                      ("LC_ALL=C.UTF-8", "changes how bash reads the rest of the script")])
+def test_config_line_that_is_refused(ref_root, line, why):
+    """Exports whose effect on bash itself (or on what children inherit) is not restated stop the run with status 2."""
+    sc = Scenario(name="exportrefused", stdin="\n-e a\\\\n%s\\\\nQ=\n\n\n\n\n\n\nyes\n" % line)
+    mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert mine.exit_status == 2 and why in mine.stderr and "refusing to go on: a line of ./config exports" in mine.stderr
+    assert not [c for c in mine.calls if c.startswith("terraform")]
+
+
+def test_cdpath_that_leaves_the_workspace_is_refused(ref_root, tmp_path):
+    (tmp_path / "elsewhere" / "terraform").mkdir(parents=True)
+    sc = Scenario(name="cdpathaway", stdin="\n" * 8 + "yes\n", env={"CDPATH": str(tmp_path / "elsewhere")})
+    mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert mine.exit_status == 2 and "CDPATH takes `cd terraform` to" in mine.stderr

@@ -409,3 +409,35 @@ def echo_unquoted(value: str, cwd: str) -> str:
     """``echo $value`` -- the workhorse of the reference (unquoted on purpose
     there or not, it is what decides the bytes)."""
     return echo_builtin(expand_unquoted(value, cwd), getattr(cwd, "utf8", False))
+
+
+# --------------------------------------------------------------------------
+# how `export -p` / `declare -p` print a value (bash: show_var_attributes ->
+# ansic_shouldquote / ansic_quote / sh_double_quote)
+# --------------------------------------------------------------------------
+_ANSIC_NAMES = {0x1B: "\\E", 7: "\\a", 8: "\\b", 12: "\\f", 10: "\\n", 13: "\\r", 9: "\\t", 11: "\\v", 92: "\\\\", 39: "\\'"}
+
+
+def _wide_printable(c: str) -> bool:
+    import unicodedata
+    return unicodedata.category(c) not in ("Cc", "Cs", "Cn", "Zl", "Zp")
+
+
+def declare_value(value: str, utf8: bool = False) -> str:
+    """``"value"`` with ``" $ ` \\`` escaped -- or, when the value holds anything the locale cannot print,
+    ``$'...'`` with C escapes and three-digit octal for the bytes of what is not printable."""
+    def printable(c: str) -> bool:
+        if ord(c) < 0x80:
+            return 0x20 <= ord(c) < 0x7F
+        return utf8 and not "\udc80" <= c <= "\udcff" and _wide_printable(c)
+    if all(printable(c) for c in value):
+        return '"' + "".join("\\" + c if c in '"$`\\' else c for c in value) + '"'
+    out = []
+    for c in value:
+        if ord(c) in _ANSIC_NAMES:
+            out.append(_ANSIC_NAMES[ord(c)])
+        elif printable(c):
+            out.append(c)
+        else:
+            out.append("".join("\\%03o" % b for b in to_bytes(c)))
+    return "$'" + "".join(out) + "'"

@@ -125,6 +125,15 @@ EDGE: List[Scenario] = [
              note="... '-en': the script is 'np' -- extra characters after command"),
     Scenario(name="pkg_index_word_is_sed_options_eE", stdin=_answers("", "", "", "", "", "", "", "-e \\\\055eE 1", "", "yes"),
              note="... '-eE': the script is 'Ep' -- unknown command: `E'"),
+    Scenario(name="cfg_line_is_export_p", stdin=_answers("", "-e a\\\\n-p\\\\nQ=", "", "", "", "", "", "", "", "yes"),
+             note="a description of three lines puts a line '-p' into ./config: `export \"-p\"` lists every exported variable on "
+                  "stdout (declare -x ..., the ones without a value by name only) and the run goes on (setup.sh:546)"),
+    Scenario(name="cfg_line_is_an_invalid_export_option", stdin=_answers("", "-e a\\\\n-n X\\\\nQ=", "", "", "", "", "", "", "", "yes"),
+             note="... '-n X' is one word: the options n, ' ', X -- `export: - : invalid option`, usage, status 2, errexit"),
+    Scenario(name="cfg_line_exports_a_name_without_value", stdin=_answers("", "-e a\\\\ni\\\\nQ=", "", "", "", "", "", "", "", "yes"),
+             note="... 'i': the loop counter of setup.sh:148 has the export attribute from then on, terraform sees i=2"),
+    Scenario(name="cfg_line_assigns_a_readonly_variable", stdin=_answers("", "-e a\\\\nUID=0\\\\nQ=", "", "", "", "", "", "", "", "yes"),
+             note="... 'UID=0': `./setup.sh: line 546: UID: readonly variable`, status 1, errexit; config.tmp stays behind"),
     Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
              stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
     Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),
@@ -466,6 +475,9 @@ EDGE += [
     Scenario(name="text_unicode_escapes_in_the_c_locale", stdin=_answers("-e caf\\\\u00e9 \\\\U0001F600", "-e \\\\ud800 \\\\u41", "", "", "", "", "", "", "yes"),
              networks=triton_table([("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4"), ("caf\\u00e9", "0b206464-d655-4723-a848-86d0f28764c8")]),
              note="... in the C locale only ASCII can be written: \\u00e9 comes back as \\u00E9, \\u41 is A"),
+    Scenario(name="env_cdpath_names_the_workspace", stdin=BLANK8 + YES, env={"CDPATH": "/nonexistent:.:<SBX>/ws"},
+             note="CDPATH is searched before the current directory; `cd terraform` / `cd ansible` found through the non-empty "
+                  "entry '.' announce the new directory on stdout (three extra lines)"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

@@ -46,7 +46,7 @@ from . import sedprog
 from . import textops as tx
 from .basharith import ArithAbort, ArithError, ArithFatal, ArithRefused, Evaluator
 from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
-from .tritonenv import CommandNotFound, InvalidIdentifier, TritonEnvError, apply_triton_env
+from .tritonenv import SHELL_BEHAVIOUR, CommandNotFound, InvalidIdentifier, TritonEnvError, apply_triton_env
 
 RULE = "#" * 80
 DASHES = "---------------"
@@ -57,10 +57,42 @@ INDEX_RE = r"^[1-9][0-9]*$"                                  # setup.sh:428
 _IDENT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
 
 #: environment variables that configure this program and nothing else
+#: `export NAME=value` on these fails: bash made them read-only at start-up
+_READONLY = frozenset(["UID", "EUID", "PPID", "SHELLOPTS", "BASHOPTS", "BASH_VERSINFO"])
+#: what bash computes each time it is asked, or once at start-up from things this program does not know: children
+#: would see *that* value, whatever the line of ./config assigned
+_NOT_MODELLED = frozenset([
+    "RANDOM", "SRANDOM", "SECONDS", "EPOCHSECONDS", "EPOCHREALTIME", "BASHPID", "BASH_COMMAND", "BASH_LINENO", "BASH_SOURCE",
+    "BASH_ARGC", "BASH_ARGV", "BASH_ARGV0", "BASH_SUBSHELL", "FUNCNAME", "GROUPS", "DIRSTACK", "PIPESTATUS", "HISTCMD", "LINENO",
+    "COMP_WORDBREAKS", "BASH_ALIASES", "BASH_CMDS", "BASH_REMATCH"])
+#: ... and what it sets once at start-up: known again as soon as the line assigns a value
+_SET_AT_STARTUP = frozenset(["SHELLOPTS", "BASHOPTS", "BASH_VERSINFO", "BASH", "BASH_VERSION", "HOSTNAME", "HOSTTYPE", "MACHTYPE",
+                             "OSTYPE", "PS4", "SHELL", "TERM", "PATH"])
+
 OWN_ENV = ("TK8S_PROGRAM", "TK8S_CACHE_TRITON", "TK8S_INPROCESS_CLOCK")
 
 TRITON_NETWORKS = ["triton", "networks", "-oname,id"]
 TRITON_PACKAGES = ["triton", "packages", "-oname,id"]
+
+
+#: `export --help` of bash 5.2 (a line of ./config can be exactly that)
+_EXPORT_HELP = (
+    'export: export [-fn] [name[=value] ...] or export -p\n'
+    '    Set export attribute for shell variables.\n'
+    '    \n'
+    '    Marks each NAME for automatic export to the environment of subsequently\n'
+    '    executed commands.  If VALUE is supplied, assign VALUE before exporting.\n'
+    '    \n'
+    '    Options:\n'
+    '      -f\trefer to shell functions\n'
+    '      -n\tremove the export property from each NAME\n'
+    '      -p\tdisplay a list of all exported variables and functions\n'
+    '    \n'
+    "    An argument of `--' disables further option processing.\n"
+    '    \n'
+    '    Exit Status:\n'
+    '    Returns success unless an invalid option is given or NAME is invalid.\n'
+)
 
 
 class _ShellVars(dict):
@@ -197,6 +229,9 @@ class Supervisor:
     def cd(self, rel: str) -> None:
         """``cd rel``: no process of ours changes directory (children are started
         with ``cwd=``), but PWD and OLDPWD are part of what they inherit."""
+        target = os.path.normpath(os.path.join(self._cwd, rel))
+        if self.v.get("CDPATH") and not rel.startswith(("/", "./", "../")) and rel not in (".", ".."):
+            target = self._cd_through_cdpath(rel, target)
         # plain assignments: both are exported because bash gave them the attribute at
         # start-up, and stop being so once `triton env` has unset them
         if "PWD" in self.v:
@@ -209,8 +244,31 @@ class Supervisor:
             if exported:
                 self.v.export_when_set.discard("OLDPWD")
                 self.rt.env["OLDPWD"] = ""
-        self._cwd = os.path.normpath(os.path.join(self._cwd, rel))
+        self._cwd = target
         self.v["PWD"] = self._cwd
+
+    def _cd_through_cdpath(self, rel: str, plain: str) -> str:
+        """CDPATH (inherited, or exported by a line of ./config) is searched before the current directory, and a
+        directory found through a non-empty entry is announced on stdout.  An entry that leads back into the
+        workspace is followed; one that leads anywhere else would move the whole run and is refused."""
+        home = self.v.get("HOME", "")
+        for entry in self.v["CDPATH"].split(":"):
+            where = entry
+            if entry == "~" or entry.startswith("~/"):
+                where = home + entry[1:]
+            elif entry.startswith("~"):
+                continue                              # ~user: the password database is not consulted for this
+            found = os.path.normpath(os.path.join(self._cwd, where, rel))
+            if not os.path.isdir(found):
+                continue
+            if entry == "":
+                return plain
+            if os.path.realpath(found) != os.path.realpath(plain):
+                self.rt.err("%s: refusing to go on: CDPATH takes `cd %s` to %s, out of the workspace\n" % (self.program, rel, found))
+                raise ScriptExit(2)
+            self.write_out(found + "\n")
+            return found
+        return plain
 
     # ------------------------------------------------------------------
     # small helpers: the shell idioms the reference repeats
@@ -867,6 +925,8 @@ class Supervisor:
         os.remove(self.rt.path("config.tmp"))
 
     def _export(self, word: str) -> None:
+        if len(word) > 1 and word.startswith("-"):
+            return self._export_options(word)
         name, eq, value = word.partition("=")
         append = name.endswith("+") and bool(eq)
         if append:
@@ -874,10 +934,45 @@ class Supervisor:
         if not _IDENT.fullmatch(name):
             self.rt.err("%s: line 546: export: `%s': not a valid identifier\n" % (self.program, word))
             raise ScriptExit(1)
+        if eq and name in _READONLY:
+            self.rt.err("%s: %s: readonly variable\n" % (self.at(546), name))
+            raise ScriptExit(1)
+        if name in _NOT_MODELLED or (eq and name in SHELL_BEHAVIOUR) or (not eq and name in _SET_AT_STARTUP and name not in self.v):
+            self.rt.err("%s: refusing to go on: a line of ./config exports %s, which %s\n"
+                        % (self.program, name, "changes how bash reads the rest of the script" if name in SHELL_BEHAVIOUR
+                           else "bash computes by itself (its value is not restated here)"))
+            raise ScriptExit(2)
         if eq:
             self.v[name] = (self.v.get(name, "") + value) if append else value
         if name in self.v:
             self.rt.env[name] = self.v[name]
+        elif self._bash_variable(name) is not None:
+            self.rt.env[name] = self._bash_variable(name)       # UID, PPID, IFS ...: bash has a value for it
+        else:
+            self.v.export_when_set.add(name)    # the attribute waits for a value (`i`, `master` ... get one later)
+
+    def _export_options(self, word: str) -> None:
+        """``export "-..."``: a line of ./config that begins with a dash is the *options* of export (one word, so
+        there are no names behind them).  ``-p``, ``-n``, ``--`` list what is exported; ``-f``/``-a``/``-A`` list
+        the exported functions/arrays, of which there are none; any other letter is a usage error, status 2."""
+        if word == "--help":
+            self.write_out(_EXPORT_HELP, 546)
+            raise ScriptExit(2)
+        if word != "--":
+            for flag in word[1:]:
+                if flag not in "aAfnp":
+                    self.rt.err("%s: export: -%s: invalid option\nexport: usage: export [-fn] [name[=value] ...] or export -p\n"
+                                % (self.at(546), flag))
+                    raise ScriptExit(2)
+            if any(flag in "aAf" for flag in word[1:]):
+                return
+        env, pending = self.rt.env, self.v.export_when_set
+        listing = []
+        for name in sorted((set(env) | pending) - {"_"}, key=sh.to_bytes):
+            if not _IDENT.fullmatch(name):
+                continue                            # never became a shell variable
+            listing.append("declare -x %s=%s\n" % (name, sh.declare_value(env[name], self.utf8)) if name in env else "declare -x %s\n" % name)
+        self.write_out("".join(listing), 546)
 
     # ------------------------------------------------------------------
     # a10-a13  Terraform root config + run  (setup.sh:138-198)
