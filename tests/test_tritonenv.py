@@ -163,3 +163,42 @@ def test_a_command_that_does_not_exist_gets_bashs_answer():
         with pytest.raises(TritonEnvError) as exc:
             apply_triton_env(text, {}, {}, exists=lambda name: name == "ls")
         assert not isinstance(exc.value, CommandNotFound), text
+
+
+def _bash_says(text):
+    p = subprocess.run(["bash", "-c", 'set -e; eval "$1"; echo survived', "_", text], capture_output=True,
+                       env=dict(START, PATH="/usr/bin:/bin", LC_ALL="C"))
+    return p.returncode, [line.split(": ", 2)[2] if line.startswith("_: line") else line for line in p.stderr.decode().splitlines()]
+
+
+@pytest.mark.parametrize("text", ["export UID=5\n", "UID=5\n", "export A=1 UID=5 EUID=6 B=2\n", "unset UID\n", "unset A PPID B\n",
+                                  "export SHELLOPTS=x\n", "BASHOPTS=y\n", "unset 1x UID\n", "export 1x UID=3 2y\n"])
+def test_read_only_variables_get_bashs_answer(text):
+    """Not refusals: bash answers these itself (status 1), running nothing."""
+    from tritonk8ssupervisor_b200.tritonenv import BashDiagnostic
+    status, said = _bash_says(text)
+    assert status == 1
+    with pytest.raises(BashDiagnostic) as exc:
+        apply_triton_env(text, dict(START), dict(START))
+    assert exc.value.messages() == said
+
+
+@pytest.mark.parametrize("text", ["export RANDOM=3\n", "SECONDS=1\n", "export LINENO\n", "unset RANDOM\n", "export A=$RANDOM\n", "A=$HOSTNAME\n",
+                                  "export HOSTNAME\n", "export BASH_VERSION\n", "export -p\n", "export -n A\n", "unset -v A\n", "unset -f A\n",
+                                  "export A=${BASH_VERSION}\n", "export FUNCNAME\n", "export PS4\n"])
+def test_what_bash_computes_by_itself_is_refused(text):
+    from tritonk8ssupervisor_b200.tritonenv import BashDiagnostic
+    with pytest.raises(TritonEnvError) as exc:
+        apply_triton_env(text, dict(START), dict(START))
+    assert not isinstance(exc.value, BashDiagnostic) and "refusing" in str(exc.value)
+
+
+def test_variables_bash_provides_expand_to_their_values():
+    import os
+    shell, env = dict(START), dict(START)
+    provided = {"UID": str(os.getuid()), "IFS": " \t\n", "OPTIND": "1"}.get
+    apply_triton_env('export A="$UID/$OPTIND" B=$NOSUCH\nexport UID\nHOSTNAME=h\nexport HOSTNAME\n', shell, env, provided=provided)
+    assert env["A"] == "%d/1" % os.getuid() and env["B"] == "" and env["UID"] == str(os.getuid()) and env["HOSTNAME"] == "h"
+    out = subprocess.run(["bash", "-c", 'eval "$1"; echo "$A|$B"; env | grep -c "^UID="', "_", 'export A="$UID/$OPTIND" B=$NOSUCH\nexport UID\n'],
+                         capture_output=True, env=dict(START, PATH="/usr/bin:/bin")).stdout.decode().split()
+    assert out == ["%d/1|" % os.getuid(), "1"]

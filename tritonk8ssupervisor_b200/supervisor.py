@@ -46,7 +46,8 @@ from . import sedprog
 from . import textops as tx
 from .basharith import ArithAbort, ArithError, ArithFatal, ArithRefused, Evaluator
 from .runtime import CAPTURE, DEVNULL, TO_STDOUT, Runtime, ScriptExit
-from .tritonenv import SHELL_BEHAVIOUR, CommandNotFound, InvalidIdentifier, TritonEnvError, apply_triton_env
+from .tritonenv import (NOT_MODELLED as _NOT_MODELLED, READONLY as _READONLY, SET_AT_STARTUP as _SET_AT_STARTUP, SHELL_BEHAVIOUR,
+                        BashDiagnostic, CommandNotFound, TritonEnvError, apply_triton_env)
 
 RULE = "#" * 80
 DASHES = "---------------"
@@ -57,18 +58,6 @@ INDEX_RE = r"^[1-9][0-9]*$"                                  # setup.sh:428
 _IDENT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
 
 #: environment variables that configure this program and nothing else
-#: `export NAME=value` on these fails: bash made them read-only at start-up
-_READONLY = frozenset(["UID", "EUID", "PPID", "SHELLOPTS", "BASHOPTS", "BASH_VERSINFO"])
-#: what bash computes each time it is asked, or once at start-up from things this program does not know: children
-#: would see *that* value, whatever the line of ./config assigned
-_NOT_MODELLED = frozenset([
-    "RANDOM", "SRANDOM", "SECONDS", "EPOCHSECONDS", "EPOCHREALTIME", "BASHPID", "BASH_COMMAND", "BASH_LINENO", "BASH_SOURCE",
-    "BASH_ARGC", "BASH_ARGV", "BASH_ARGV0", "BASH_SUBSHELL", "FUNCNAME", "GROUPS", "DIRSTACK", "PIPESTATUS", "HISTCMD", "LINENO",
-    "COMP_WORDBREAKS", "BASH_ALIASES", "BASH_CMDS", "BASH_REMATCH"])
-#: ... and what it sets once at start-up: known again as soon as the line assigns a value
-_SET_AT_STARTUP = frozenset(["SHELLOPTS", "BASHOPTS", "BASH_VERSINFO", "BASH", "BASH_VERSION", "HOSTNAME", "HOSTTYPE", "MACHTYPE",
-                             "OSTYPE", "PS4", "SHELL", "TERM", "PATH"])
-
 OWN_ENV = ("TK8S_PROGRAM", "TK8S_CACHE_TRITON", "TK8S_INPROCESS_CLOCK")
 
 TRITON_NETWORKS = ["triton", "networks", "-oname,id"]
@@ -490,11 +479,12 @@ class Supervisor:
         rt, v = self.rt, self.v
         _, text = rt.run(["triton", "env"], stdout=CAPTURE, where=self.at(210), lone_subst=True)  # status is swallowed by eval "$(...)"
         try:
-            apply_triton_env(self.subst(text, 210), v, rt.env, home=rt.passwd_home, exists=rt.command_exists)
+            apply_triton_env(self.subst(text, 210), v, rt.env, home=rt.passwd_home, exists=rt.command_exists,
+                             provided=self._bash_variable)
         except CommandNotFound as exc:
             rt.err("%s: %s\n" % (self.at(210 + exc.line), exc))
             raise ScriptExit(127)
-        except InvalidIdentifier as exc:
+        except BashDiagnostic as exc:
             # bash's own verdict, not a refusal: eval numbers the lines of its text from the line it stands on
             for message in exc.messages():
                 rt.err("%s: %s\n" % (self.at(210 + exc.line), message))

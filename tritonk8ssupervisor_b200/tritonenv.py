@@ -52,18 +52,27 @@ def ansic_quote(text: str) -> str:
     return "$'" + "".join(names.get(b) or (chr(b) if 0x20 <= b < 0x7F else "\\%03o" % b) for b in data) + "'"
 
 
-class InvalidIdentifier(TritonEnvError):
+class BashDiagnostic(TritonEnvError):
+    """Not a refusal: what bash itself says to the command without running anything (status 1, which errexit
+    makes the script's).  ``line`` is the 0-based line of the text the command started on."""
+
+    def __init__(self, messages: List[str], line: int):
+        super().__init__("; ".join(messages))
+        self._messages, self.line = list(messages), line
+
+    def messages(self) -> List[str]:
+        return list(self._messages)
+
+
+class InvalidIdentifier(BashDiagnostic):
     """``export WORD`` where WORD is no ``NAME[=value]``: not a refusal -- bash itself
     rejects it (``export: `WORD': not a valid identifier``, status 1, which errexit makes
     the script's).  ``line`` is the 0-based line of the text the command started on."""
 
     def __init__(self, words: List[str], line: int):
-        super().__init__("; ".join("export: `%s': not a valid identifier" % w for w in words))
+        super().__init__(["export: `%s': not a valid identifier" % w for w in words], line)
         #: every word of the command that was rejected (the valid ones have taken effect)
-        self.words, self.line = words, line
-
-    def messages(self) -> List[str]:
-        return ["export: `%s': not a valid identifier" % w for w in self.words]
+        self.words = words
 
 
 #: variables that change how bash reads the *rest of the script* (field splitting,
@@ -73,9 +82,33 @@ SHELL_BEHAVIOUR = frozenset(["IFS", "GLOBIGNORE", "POSIXLY_CORRECT", "BASH_COMPA
                              "LC_ALL", "LC_COLLATE", "LC_CTYPE", "LANG"])
 
 
+#: assigning to these, or unsetting them, fails: bash made them read-only at start-up
+READONLY = frozenset(["UID", "EUID", "PPID", "SHELLOPTS", "BASHOPTS", "BASH_VERSINFO"])
+#: what bash computes each time it is asked: children would see *that* value, whatever was assigned
+NOT_MODELLED = frozenset([
+    "RANDOM", "SRANDOM", "SECONDS", "EPOCHSECONDS", "EPOCHREALTIME", "BASHPID", "BASH_COMMAND", "BASH_LINENO", "BASH_SOURCE",
+    "BASH_ARGC", "BASH_ARGV", "BASH_ARGV0", "BASH_SUBSHELL", "FUNCNAME", "GROUPS", "DIRSTACK", "PIPESTATUS", "HISTCMD", "LINENO",
+    "COMP_WORDBREAKS", "BASH_ALIASES", "BASH_CMDS", "BASH_REMATCH"])
+#: ... and what it sets once at start-up from things this program does not know: known again once assigned
+SET_AT_STARTUP = frozenset(["SHELLOPTS", "BASHOPTS", "BASH_VERSINFO", "BASH", "BASH_VERSION", "HOSTNAME", "HOSTTYPE", "MACHTYPE",
+                            "OSTYPE", "PS4", "SHELL", "TERM", "PATH"])
+
+
 def _guard(name: str) -> None:
     if name in SHELL_BEHAVIOUR:
         raise TritonEnvError("refusing to let `triton env` output change %s: it alters how the rest of the script is read" % name)
+    if name in NOT_MODELLED:
+        raise TritonEnvError("refusing to let `triton env` output touch %s: bash computes it by itself (its value is not restated here)" % name)
+
+
+def _lookup(name: str, shell_vars: Dict[str, str], provided: Optional[Callable[[str], Optional[str]]]) -> str:
+    """``$NAME``: a shell variable, else one of the few bash provides by itself that have a known value."""
+    if name in shell_vars:
+        return shell_vars[name]
+    if name in NOT_MODELLED or name in SET_AT_STARTUP:
+        raise TritonEnvError("refusing to expand $%s in `triton env` output: bash computes it by itself (its value is not restated here)" % name)
+    value = provided(name) if provided is not None else None
+    return "" if value is None else value
 
 
 class _Var:
@@ -210,7 +243,8 @@ def _default_home() -> str:
         return "/"
 
 
-def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[], str]) -> Optional[Tuple[str, Optional[str]]]:
+def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[], str],
+                provided: Optional[Callable[[str], Optional[str]]] = None) -> Optional[Tuple[str, Optional[str]]]:
     """(name, value) when the word is ``NAME=...`` (value None for a bare ``NAME``);
     None when it is not an assignment word.  The value is expanded the way bash
     expands an assignment: parameter references without field splitting or
@@ -232,7 +266,7 @@ def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[
     while i < len(rest):
         p = rest[i]
         if isinstance(p, _Var):
-            out.append(shell_vars.get(p.name, ""))
+            out.append(_lookup(p.name, shell_vars, provided))
             at_start = False
             i += 1
             continue
@@ -267,11 +301,13 @@ def _assignment(word: List[_Piece], shell_vars: Dict[str, str], home: Callable[[
 
 def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                      home: Optional[Callable[[], str]] = None,
-                     exists: Optional[Callable[[str], bool]] = None) -> None:
+                     exists: Optional[Callable[[str], bool]] = None,
+                     provided: Optional[Callable[[str], Optional[str]]] = None) -> None:
     """Mutate ``shell_vars`` (all shell variables) and ``env`` (the exported
     ones) as ``eval`` of ``text`` would for the supported dialect.  ``home()``
     is what ``~`` stands for when ``HOME`` is not among the shell variables;
-    ``exists(name)`` says whether a command of that name can be found on PATH."""
+    ``exists(name)`` says whether a command of that name can be found on PATH;
+    ``provided(name)`` is the value of a variable bash sets by itself (UID, PPID, IFS ...), if it is known."""
     def tilde_home() -> str:
         if "HOME" in shell_vars:
             return shell_vars["HOME"]
@@ -293,33 +329,54 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
             if len(words) == 1:
                 # a bare `export` lists every exported variable on the script's stdout
                 raise TritonEnvError("refusing to run a bare `export` from `triton env` output")
-            rejected: List[str] = []
+            said: List[str] = []
             for w in words[1:]:
-                parsed = _assignment(w, shell_vars, tilde_home)
+                if not isinstance(w[0], _Var) and w[0] == ("-", False):
+                    raise TritonEnvError("refusing to run `export` with options from `triton env` output: %r" % _show(w))
+                parsed = _assignment(w, shell_vars, tilde_home, provided)
                 if parsed is None:
                     if any(isinstance(p, _Var) for p in w):
                         raise TritonEnvError("not a valid identifier in `triton env` output: %r" % _show(w))
-                    rejected.append(_show(w))
+                    said.append("export: `%s': not a valid identifier" % _show(w))
                     continue
                 name, value = parsed
                 _guard(name)
+                if value is not None and name in READONLY:
+                    # under errexit (setup.sh:3) the first of these is the last thing bash says
+                    raise BashDiagnostic(said + ["%s: readonly variable" % name], line)
                 if value is not None:
                     shell_vars[name] = value
                 if name in shell_vars:
                     env[name] = shell_vars[name]
+                elif name in SET_AT_STARTUP:
+                    raise TritonEnvError("refusing to export %s from `triton env` output: bash computes it by itself (its value is not restated here)" % name)
+                elif provided is not None and provided(name) is not None:
+                    env[name] = provided(name)      # UID, PPID, IFS ...: bash has a value for it
                 else:
                     pending.add(name)           # `export NAME` before NAME has a value: exported once it gets one
-            if rejected:
-                raise InvalidIdentifier(rejected, line)
+            if said:
+                if all(m.startswith("export: `") for m in said):
+                    raise InvalidIdentifier([m[len("export: `"):-len("': not a valid identifier")] for m in said], line)
+                raise BashDiagnostic(said, line)
         elif head == "unset":
+            said = []
             for w in words[1:]:
                 name = plain(w)
+                if name.startswith("-"):
+                    raise TritonEnvError("refusing to run `unset` with options from `triton env` output: %r" % name)
+                if not _NAME.fullmatch(name):
+                    continue                    # bash (not in posix mode) looks for a function of that name, silently
                 _guard(name)
+                if name in READONLY:
+                    said.append("unset: %s: cannot unset: readonly variable" % name)
+                    continue
                 shell_vars.pop(name, None)
                 env.pop(name, None)
                 pending.discard(name)
+            if said:
+                raise BashDiagnostic(said, line)
         else:
-            parsed = _assignment(words[0], shell_vars, tilde_home) if len(words) == 1 else None
+            parsed = _assignment(words[0], shell_vars, tilde_home, provided) if len(words) == 1 else None
             if parsed is None or parsed[1] is None:
                 # a command.  One that cannot be found runs nothing, and bash's answer to it can be
                 # given without running anything; every other command is refused.
@@ -330,6 +387,8 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                 raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(_show(w) for w in words))
             name, value = parsed
             _guard(name)
+            if name in READONLY:
+                raise BashDiagnostic(["%s: readonly variable" % name], line)
             shell_vars[name] = value
             if name in env or name in pending:
                 pending.discard(name)
