@@ -478,6 +478,9 @@ EDGE += [
     Scenario(name="env_cdpath_names_the_workspace", stdin=BLANK8 + YES, env={"CDPATH": "/nonexistent:.:<SBX>/ws"},
              note="CDPATH is searched before the current directory; `cd terraform` / `cd ansible` found through the non-empty "
                   "entry '.' announce the new directory on stdout (three extra lines)"),
+    Scenario(name="env_opterr_is_reset", stdin=BLANK8 + YES, env={"OPTERR": "0", "OPTIND": "7"},
+             note="bash sets OPTERR=1 and OPTIND=1 at start-up whatever it inherits; the export attribute stays, so that is what "
+                  "terraform and ansible-playbook find in their environment"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

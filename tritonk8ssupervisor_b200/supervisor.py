@@ -143,6 +143,13 @@ class Supervisor:
             self.rt.err("bash: warning: shell level (%d) too high, resetting to 1\n" % level)
             level = 1
         self.export("SHLVL", str(level))
+        # inherited values bash overwrites at start-up (the export attribute stays)
+        if "OPTERR" in env:
+            self.v["OPTERR"] = "1"
+        if "PPID" in env:
+            self.v["PPID"] = str(os.getppid())
+        if "PS4" in env and os.geteuid() == 0:
+            self.v["PS4"] = "+ "                      # root does not inherit PS4
         root = os.path.abspath(self.root)
         pwd = env.get("PWD", "")
         try:
