@@ -146,6 +146,8 @@ class Supervisor:
         # inherited values bash overwrites at start-up (the export attribute stays)
         if "OPTERR" in env:
             self.v["OPTERR"] = "1"
+        if "OPTIND" in env:
+            self.v["OPTIND"] = "1"
         if "PPID" in env:
             self.v["PPID"] = str(os.getppid())
         if "PS4" in env and os.geteuid() == 0:
