@@ -384,3 +384,29 @@ def test_cdpath_that_leaves_the_workspace_is_refused(ref_root, tmp_path):
     sc = Scenario(name="cdpathaway", stdin="\n" * 8 + "yes\n", env={"CDPATH": str(tmp_path / "elsewhere")})
     mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
     assert mine.exit_status == 2 and "CDPATH takes `cd terraform` to" in mine.stderr
+
+
+# --- answers of several lines: each extra line becomes a line of ./config, i.e. an argument of `export` ---
+_CFG_PIECES = ["A", "B", "i", "=", "=", "+=", "[0]", "[", "]", " ", "-", "-p", "-n", "-f", "--", "x", "1", "_", "$A", "$(id)", "`id`", "*", "?", "'",
+               '"', "\\\\\\\\", "#", ";", "&", "|", "~", "é", "\udcff", "KUBERNETES_NAME", "KUBERNETES_NUMBER_OF_NODES=2", "HOME=/x", "PWD",
+               "OLDPWD=", "SHLVL=x", "master", "network=", "tmp", "CDPATH=.", "UID", "OPTIND=", "\\\\\\\\t", "\\\\\\\\x41", "-e", "\\\\\\\\055"]
+
+
+def make_config_lines(seed: int) -> Scenario:
+    import dataclasses
+    sc = make(seed)
+    r = random.Random(seed * 23 + 11)
+    answers = [""] * 9
+    for _ in range(r.randint(1, 3)):
+        lines = ["".join(r.choice(_CFG_PIECES) for _ in range(r.randint(1, 5))) for _ in range(r.randint(1, 3))]
+        answers[r.choice([0, 1, 2, 3])] = "-e a" + "".join("\\\\n" + line for line in lines) + r.choice(["", "\\\\nQ="])
+    kw = {"stdin": "\n".join(answers) + "\n" + r.choice(["yes\n", "yes"])}
+    if seed % 3 == 0:
+        kw["env"] = dict(sc.env, LANG="C.UTF-8")
+        kw["unset_env"] = ["LC_ALL"]
+    return dataclasses.replace(sc, **kw)
+
+
+@pytest.mark.parametrize("block", range(2))
+def test_property_fuzzed_config_lines(ref_root, block):
+    assert _sweep(ref_root, make_config_lines, range(70 + 12 * block, 70 + 12 * (block + 1))) == []

@@ -185,7 +185,7 @@ def test_read_only_variables_get_bashs_answer(text):
 
 @pytest.mark.parametrize("text", ["export RANDOM=3\n", "SECONDS=1\n", "export LINENO\n", "unset RANDOM\n", "export A=$RANDOM\n", "A=$HOSTNAME\n",
                                   "export HOSTNAME\n", "export BASH_VERSION\n", "export -p\n", "export -n A\n", "unset -v A\n", "unset -f A\n",
-                                  "export A=${BASH_VERSION}\n", "export FUNCNAME\n", "export PS4\n"])
+                                  "export A=${BASH_VERSION}\n", "export FUNCNAME\n", "export PS4\n", "OPTIND=1+1\n", "export OPTIND=x\n"])
 def test_what_bash_computes_by_itself_is_refused(text):
     from tritonk8ssupervisor_b200.tritonenv import BashDiagnostic
     with pytest.raises(TritonEnvError) as exc:

@@ -941,6 +941,13 @@ class Supervisor:
                         % (self.program, name, "changes how bash reads the rest of the script" if name in SHELL_BEHAVIOUR
                            else "bash computes by itself (its value is not restated here)"))
             raise ScriptExit(2)
+        if eq and name == "OPTIND":
+            # an integer variable: what is assigned is the value of the text as an arithmetic expression
+            number = self.arith_eval(value, 546, "export")
+            if number is None:
+                raise ScriptExit(1)
+            value = str(number + (int(self._arith_get("OPTIND") or 0) if append else 0))
+            append = False
         if eq:
             self.v[name] = (self.v.get(name, "") + value) if append else value
         if name in self.v:

@@ -84,6 +84,8 @@ SHELL_BEHAVIOUR = frozenset(["IFS", "GLOBIGNORE", "POSIXLY_CORRECT", "BASH_COMPA
 
 #: assigning to these, or unsetting them, fails: bash made them read-only at start-up
 READONLY = frozenset(["UID", "EUID", "PPID", "SHELLOPTS", "BASHOPTS", "BASH_VERSINFO"])
+#: integer variables: what is assigned to them is evaluated as an arithmetic expression first
+INTEGER = frozenset(["OPTIND"])
 #: what bash computes each time it is asked: children would see *that* value, whatever was assigned
 NOT_MODELLED = frozenset([
     "RANDOM", "SRANDOM", "SECONDS", "EPOCHSECONDS", "EPOCHREALTIME", "BASHPID", "BASH_COMMAND", "BASH_LINENO", "BASH_SOURCE",
@@ -341,6 +343,8 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                     continue
                 name, value = parsed
                 _guard(name)
+                if value is not None and name in INTEGER:
+                    raise TritonEnvError("refusing to assign %s from `triton env` output: bash would evaluate the value as arithmetic" % name)
                 if value is not None and name in READONLY:
                     # under errexit (setup.sh:3) the first of these is the last thing bash says
                     raise BashDiagnostic(said + ["%s: readonly variable" % name], line)
@@ -387,6 +391,8 @@ def apply_triton_env(text: str, shell_vars: Dict[str, str], env: Dict[str, str],
                 raise TritonEnvError("refusing to run a command from `triton env` output: %r" % " ".join(_show(w) for w in words))
             name, value = parsed
             _guard(name)
+            if name in INTEGER:
+                raise TritonEnvError("refusing to assign %s from `triton env` output: bash would evaluate the value as arithmetic" % name)
             if name in READONLY:
                 raise BashDiagnostic(["%s: readonly variable" % name], line)
             shell_vars[name] = value
