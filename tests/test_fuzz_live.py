@@ -410,3 +410,13 @@ def make_config_lines(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(2))
 def test_property_fuzzed_config_lines(ref_root, block):
     assert _sweep(ref_root, make_config_lines, range(70 + 12 * block, 70 + 12 * (block + 1))) == []
+
+
+def test_exported_function_named_like_a_command_is_refused(ref_root):
+    sc = Scenario(name="funcshadow", stdin="\n" * 8 + "yes\n", env={"BASH_FUNC_sleep%%": "() {  echo zzz\n}", "BASH_FUNC_ml%%": "() {  :\n}"})
+    mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert mine.exit_status == 2 and "exports a shell function named sleep" in mine.stderr and mine.calls == []
+    sc = Scenario(name="funcother", stdin="\n" * 8 + "yes\n", env={"BASH_FUNC_ml%%": "() {  :\n}"})
+    theirs = run_reference(sc, ref_root)
+    mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert theirs.diff(mine) == []

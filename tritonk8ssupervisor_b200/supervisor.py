@@ -58,6 +58,11 @@ INDEX_RE = r"^[1-9][0-9]*$"                                  # setup.sh:428
 _IDENT = re.compile(r"[A-Za-z_][A-Za-z0-9_]*")
 
 #: environment variables that configure this program and nothing else
+#: every command word of setup.sh that an imported function could shadow (its own functions are defined later and win)
+_COMMAND_WORDS = frozenset((
+    "triton ssh-keygen terraform ansible-playbook curl ssh date sleep sed grep sort tr uniq awk tail cat wc ls rm mv "
+    "echo read cd export eval let local exit return true false break set [ source .").split())
+
 OWN_ENV = ("TK8S_PROGRAM", "TK8S_CACHE_TRITON", "TK8S_INPROCESS_CLOCK")
 
 TRITON_NETWORKS = ["triton", "networks", "-oname,id"]
@@ -414,6 +419,13 @@ class Supervisor:
 
     def _main(self, argv: Sequence[str]) -> None:
         rt = self.rt
+        # a function exported by the caller (`export -f`) is defined in the script's bash before line 1, and one named
+        # like a command of the script would be run in its place
+        for key, value in rt.env.items():
+            if key.startswith("BASH_FUNC_") and key.endswith("%%") and value.startswith("() {") and key[10:-2] in _COMMAND_WORDS:
+                rt.err("%s: refusing to go on: the environment exports a shell function named %s, which the script would run "
+                       "instead of the command\n" % (self.program, key[10:-2]))
+                raise ScriptExit(2)
         if argv and argv[0] == "-c":
             self.clean_runner()
             raise ScriptExit(0)
