@@ -175,3 +175,15 @@ def test_declare_value_in_both_locales():
             out = subprocess.run(["bash", "-c", 'V=$1; export V; export -p | grep -a "^declare -x V="', "_", v], capture_output=True,
                                  env=dict(env, PATH="/usr/bin:/bin")).stdout.decode("utf-8", "surrogateescape")
             assert "declare -x V=" + sh.declare_value(v, utf8) == out.split("\n")[0], (ascii(v), utf8)
+
+
+def test_echo_e_escapes_go_by_the_name_of_a_locale_that_is_not_installed():
+    """LC_ALL=xx.UTF-8 cannot be set, bash runs in C -- and still writes \\u00e9 as UTF-8: where wctomb() gives up it
+    asks iconv for the character set named after the dot."""
+    import subprocess
+    from tritonk8ssupervisor_b200 import bashsem as sh
+    text = "\\u00e9|\\u20ac|\\u044f|\\u65e5|\\ud800|\\U0001F600|\\U00110000|\\u41"
+    for name in ["xx", "xx.UTF-8", "xx.ISO-8859-1", "UTF-8", "en_US", "xx.foo", "xx.utf8@euro", "xx.LATIN1", "xx.KOI8-R", "xx.CP1252",
+                 "xx.ASCII", "xx.utf-8", "xx.", ".UTF-8", "xx.UTF8.x"]:
+        real = subprocess.run(["bash", "-c", 'echo -e "$1"', "_", text], capture_output=True, env={"LC_ALL": name, "PATH": "/usr/bin:/bin"}).stdout
+        assert sh.to_bytes(sh.echo_builtin(["-e", text], sh.locale_charset(name))) == real, name

@@ -420,3 +420,24 @@ def test_exported_function_named_like_a_command_is_refused(ref_root):
     theirs = run_reference(sc, ref_root)
     mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
     assert theirs.diff(mine) == []
+
+
+# --- locale variables that disagree, or name locales that are not installed ------------------------------
+_LOCALES = [{"LC_CTYPE": "xx", "LANG": "C.UTF-8"}, {"LC_TIME": "xx", "LANG": "C.UTF-8"}, {"LC_ALL": "xx.UTF-8"}, {"LANG": "xx.UTF-8"},
+            {"LC_CTYPE": "C.UTF-8", "LANG": "xx"}, {"LC_ALL": "xx_XX.ISO-8859-1"}, {"LC_CTYPE": "C.UTF-8"}, {"LC_COLLATE": "C", "LANG": "C.UTF-8"},
+            {"LC_CTYPE": "C", "LANG": "C.UTF-8"}, {"LC_ALL": "C.UTF-8", "LANG": "xx"}]
+
+
+def make_locales(seed: int) -> Scenario:
+    import dataclasses
+    gens = (make, make_wide, make_binary, make_escapes, make_option_words, make_config_lines)
+    sc = gens[seed % len(gens)](seed)
+    loc = _LOCALES[(seed // len(gens)) % len(_LOCALES)]
+    env = {k: v for k, v in sc.env.items() if not k.startswith(("LC_", "LANG"))}
+    env.update(loc)
+    return dataclasses.replace(sc, env=env, unset_env=[] if "LC_ALL" in loc else ["LC_ALL"])
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_property_fuzzed_locale_settings(ref_root, block):
+    assert _sweep(ref_root, make_locales, range(20 * block, 20 * (block + 1))) == []

@@ -159,10 +159,13 @@ class Cwd(str):
     """A directory to expand pathnames in, which also knows whether the locale's character set is
     UTF-8 (``?`` then matches a multi-byte character as one)."""
     utf8 = False
+    #: how `echo -e` writes \\uHHHH: True (UTF-8), False (ASCII only) or the name of a character set
+    wide = False
 
-    def __new__(cls, path: str, utf8: bool = False):
+    def __new__(cls, path: str, utf8: bool = False, wide=None):
         obj = super().__new__(cls, path)
         obj.utf8 = utf8
+        obj.wide = utf8 if wide is None else wide
         return obj
 
 
@@ -316,7 +319,39 @@ def _encode_wide(value: int) -> str:
     return from_bytes(bytes(raw))
 
 
-def _echo_escapes(s: str, utf8: bool = False) -> Tuple[str, bool]:
+def locale_charset(name: str) -> str:
+    """The character set bash reads out of the *name* of a locale it could not set (or that is no multi-byte one):
+    what follows the last dot, without an @modifier; the whole name when there is no dot; ASCII for no name."""
+    if name == "":
+        return "ASCII"
+    dot = name.rfind(".")
+    if dot == -1:
+        return name
+    return name[dot + 1:].split("@", 1)[0]
+
+
+def _to_charset(value: int, charset: str) -> Optional[str]:
+    """iconv from UTF-8 to ``charset``; None when iconv knows no such character set or it has no such character.
+    (Python's codec tables stand in for glibc's: the same for UTF-8, the ISO-8859 family, KOI8, the Windows code
+    pages; corner cases of the East Asian multi-byte sets may differ.)"""
+    import codecs
+    if 0xD800 <= value <= 0xDFFF:
+        return None                                   # iconv rejects the UTF-8 of a surrogate
+    try:
+        codec = codecs.lookup(charset)
+    except LookupError:
+        return None
+    if codec.name == "utf-8":
+        return _encode_wide(value)
+    if value > 0x10FFFF:
+        return None
+    try:
+        return from_bytes(chr(value).encode(codec.name))
+    except (UnicodeEncodeError, LookupError):
+        return None
+
+
+def _echo_escapes(s: str, utf8=False) -> Tuple[str, bool]:
     """Backslash processing of ``echo -e``; returns (text, stop) where stop is
     True after ``\\c``.  ``\\uHHHH`` / ``\\UHHHHHHHH`` come out in the locale's
     character set: UTF-8 when it is that (``utf8``); in the C locale only ASCII
@@ -368,17 +403,18 @@ def _echo_escapes(s: str, utf8: bool = False) -> Tuple[str, bool]:
                     out.append(chr(value))
                 elif value > 0x7FFFFFFF:
                     pass                                   # not a code point bash can convert: nothing is written
-                elif utf8:
+                elif utf8 is True:
                     out.append(_encode_wide(value))
                 else:
-                    out.append(("\\u%04X" if value <= 0xFFFF else "\\U%08X") % value)
+                    converted = _to_charset(value, utf8) if isinstance(utf8, str) else None
+                    out.append(converted if converted is not None else ("\\u%04X" if value <= 0xFFFF else "\\U%08X") % value)
                 i = j
         else:
             out.append("\\" + d)
     return "".join(out), False
 
 
-def echo_builtin(args: Sequence[str], utf8: bool = False) -> str:
+def echo_builtin(args: Sequence[str], utf8=False) -> str:
     """Exactly what ``echo ARGS...`` writes (including the trailing newline,
     or not)."""
     newline, escapes = True, False
@@ -408,7 +444,7 @@ def cmdsubst(output: str) -> str:
 def echo_unquoted(value: str, cwd: str) -> str:
     """``echo $value`` -- the workhorse of the reference (unquoted on purpose
     there or not, it is what decides the bytes)."""
-    return echo_builtin(expand_unquoted(value, cwd), getattr(cwd, "utf8", False))
+    return echo_builtin(expand_unquoted(value, cwd), getattr(cwd, "wide", False))
 
 
 # --------------------------------------------------------------------------

@@ -481,6 +481,15 @@ EDGE += [
     Scenario(name="env_opterr_is_reset", stdin=BLANK8 + YES, env={"OPTERR": "0", "OPTIND": "7"},
              note="bash sets OPTERR=1 and OPTIND=1 at start-up whatever it inherits; the export attribute stays, so that is what "
                   "terraform and ansible-playbook find in their environment"),
+    Scenario(name="env_lc_all_names_no_installed_locale", stdin=_answers("-e caf\\\\u00e9", "", "", "", "", "", "", "", "yes"),
+             env={"LC_ALL": "xx_XX.UTF-8"},
+             note="a locale forwarded from elsewhere: bash warns (`setlocale: LC_ALL: cannot change locale`), runs in C -- and "
+                  "still writes \\u00e9 as UTF-8, because where wctomb() gives up it asks iconv for the character set in the name"),
+    Scenario(name="env_lc_ctype_invalid_lang_utf8", stdin=_answers("-e caf\\\\u00e9", "", "", "", "", "", "", "", "yes"),
+             env={"LC_CTYPE": "xx_XX", "LANG": "C.UTF-8"}, unset_env=["LC_ALL"],
+             networks=triton_table([("Joyent-SDC-Public", "31428241-4878-47d6-9fba-9a8436b596a4"), ("caf\xe9", "0b206464-d655-4723-a848-86d0f28764c8")]),
+             note="bash sets LANG for every category and skips the LC_CTYPE it cannot set: it runs in UTF-8; grep, sed and sort call "
+                  "setlocale(LC_ALL, \"\"), which fails as a whole, and run in C"),
     Scenario(name="env_path_without_usr_bin", stdin=BLANK8 + YES, env={"PATH": "<SBX>/bin:/bin"},
              note="PATH without /usr/bin"),
     Scenario(name="env_shell_level_and_directories", stdin=BLANK8 + YES,

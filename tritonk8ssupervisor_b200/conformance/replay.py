@@ -68,6 +68,20 @@ def not_reproducible_here(doc: dict) -> str:
             return "recorded for a user whose home has no .ssh; this one's is %s" % home
     if sc.get("env", {}).get("HOME") == "" and os.path.exists("/.ssh"):
         return "/.ssh exists on this machine"
+    # a fixture recorded with a locale variable naming a locale that was not installed, or one that was
+    import locale
+    for key, name in sc.get("env", {}).items():
+        if (key.startswith("LC_") or key == "LANG") and name not in ("", "C", "POSIX"):
+            saved = locale.setlocale(locale.LC_CTYPE)
+            try:
+                locale.setlocale(locale.LC_CTYPE, name)
+                installed = True
+            except locale.Error:
+                installed = False
+            finally:
+                locale.setlocale(locale.LC_CTYPE, saved)
+            if installed != (not name.startswith("xx")):
+                return "recorded where locale %s was %s" % (name, "missing" if installed else "installed")
     return ""
 
 

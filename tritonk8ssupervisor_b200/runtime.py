@@ -92,9 +92,30 @@ class Runtime:
             fh.write(bashsem.to_bytes(text))
 
     def utf8_locale(self) -> bool:
-        """Is the character set of the locale the children will run in UTF-8?  (LC_ALL, else
-        LC_CTYPE, else LANG; a locale that is not installed counts as C, as it does for them.)"""
-        name = self.env.get("LC_ALL") or self.env.get("LC_CTYPE") or self.env.get("LANG") or ""
+        """Is the character set of the locale the *children* (grep, sed, wc ...) run in UTF-8?  They call
+        ``setlocale(LC_ALL, "")``: LC_ALL if set, else every category from its LC_* variable or LANG -- and if any
+        one of those names a locale that is not installed the call fails as a whole and they run in C."""
+        env = self.env
+        if env.get("LC_ALL"):
+            return self._utf8_codeset(env["LC_ALL"])
+        for category in ("LC_COLLATE", "LC_MESSAGES", "LC_MONETARY", "LC_NUMERIC", "LC_TIME", "LC_ADDRESS", "LC_IDENTIFICATION",
+                         "LC_MEASUREMENT", "LC_NAME", "LC_PAPER", "LC_TELEPHONE"):
+            if self.locale_unavailable(env.get(category) or env.get("LANG") or ""):
+                return False
+        return self._utf8_codeset(env.get("LC_CTYPE") or env.get("LANG") or "")
+
+    def shell_utf8_locale(self) -> bool:
+        """... and the locale *bash* runs in: it sets LANG for all categories first and LC_CTYPE on top, each on
+        its own, so a variable that names no installed locale is skipped instead of spoiling the rest."""
+        env = self.env
+        if env.get("LC_ALL"):
+            return self._utf8_codeset(env["LC_ALL"])
+        ctype = env.get("LC_CTYPE") or ""
+        if ctype and not self.locale_unavailable(ctype):
+            return self._utf8_codeset(ctype)
+        return self._utf8_codeset(env.get("LANG") or "")
+
+    def _utf8_codeset(self, name: str) -> bool:
         if name in ("", "C", "POSIX"):
             return False
         import locale
@@ -104,6 +125,20 @@ class Runtime:
             return locale.nl_langinfo(locale.CODESET).upper().replace("-", "") == "UTF8"
         except locale.Error:
             return False
+        finally:
+            locale.setlocale(locale.LC_CTYPE, saved)
+
+    def locale_unavailable(self, name: str) -> bool:
+        """Would ``setlocale(LC_ALL, name)`` fail?  (bash warns about that for LC_ALL at start-up and runs in C.)"""
+        if name in ("", "C", "POSIX"):
+            return False
+        import locale
+        saved = locale.setlocale(locale.LC_CTYPE)
+        try:
+            locale.setlocale(locale.LC_CTYPE, name)
+            return False
+        except locale.Error:
+            return True
         finally:
             locale.setlocale(locale.LC_CTYPE, saved)
 
@@ -244,14 +279,17 @@ def inherited_environment() -> Dict[str, str]:
     """The environment this process was *started with*.  CPython may add
     ``LC_CTYPE=C.UTF-8`` to its own environment at start-up (locale coercion,
     when no locale is configured at all); bash does no such thing, so a variable
-    that was not there when the process was exec'ed is not passed on."""
+    that was not there when the process was exec'ed is not passed on, and one that
+    was gets the value it had."""
     env = dict(os.environ)
     if "LC_CTYPE" in env:
         try:
             with open("/proc/self/environ", "rb") as fh:
-                initial = {item.split(b"=", 1)[0] for item in fh.read().split(b"\0") if b"=" in item}
+                initial = dict(item.split(b"=", 1) for item in fh.read().split(b"\0") if b"=" in item)
             if b"LC_CTYPE" not in initial:
                 del env["LC_CTYPE"]
+            else:
+                env["LC_CTYPE"] = initial[b"LC_CTYPE"].decode("utf-8", "surrogateescape")   # `C` coerced to `C.UTF-8`
         except OSError:
             pass
     return env

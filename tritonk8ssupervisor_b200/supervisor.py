@@ -122,7 +122,13 @@ class Supervisor:
         #: the character set of the locale is UTF-8: grep then takes bytes that are not valid UTF-8 for binary data
         self.utf8 = rt.utf8_locale()
         #: where unquoted words are pathname-expanded (the workspace), with the locale's idea of a character
-        self.root = sh.Cwd(rt.root, self.utf8)
+        #: how `echo -e` writes \\uHHHH: in a locale that is not a UTF-8 one bash goes by the *name* of the locale
+        #: (LC_ALL=en_US.UTF-8 on a machine without that locale still gets UTF-8 out of it)
+        #: ... and bash itself is in such a locale (its matcher and its quoting then look at characters)
+        self.shell_utf8 = rt.shell_utf8_locale()
+        locale_name = rt.env.get("LC_ALL") or rt.env.get("LC_CTYPE") or rt.env.get("LANG") or ""
+        self.wide = True if self.shell_utf8 else sh.locale_charset(locale_name)
+        self.root = sh.Cwd(rt.root, self.shell_utf8, self.wide)
         #: shell variables (the exported ones are mirrored in ``rt.env``)
         self.v: Dict[str, str] = _ShellVars(rt.env)
         self._shell_bookkeeping()
@@ -147,6 +153,8 @@ class Supervisor:
         elif level >= 1000:
             self.rt.err("bash: warning: shell level (%d) too high, resetting to 1\n" % level)
             level = 1
+        if self.rt.locale_unavailable(env.get("LC_ALL", "")):
+            self.rt.err("bash: warning: setlocale: LC_ALL: cannot change locale (%s)\n" % env["LC_ALL"])
         self.export("SHLVL", str(level))
         # inherited values bash overwrites at start-up (the export attribute stays)
         if "OPTERR" in env:
@@ -615,7 +623,7 @@ class Supervisor:
             count += 1
             self.v["tmp"] = str(count)
             shown = sh.cmdsubst(tx.sed_sub(sh.echo_unquoted(row, self.root), r"=", "  ", count=0))
-            self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)], self.utf8), {"network": 316, "package": 409}.get(loop_var, 0))
+            self.write_out(sh.echo_builtin(["-e", "%d.\\t%s" % (count, shown)], self.wide), {"network": 316, "package": 409}.get(loop_var, 0))
             if default_prefix is not None and row.startswith(default_prefix):
                 default_at = count
         return count, default_at
@@ -749,7 +757,7 @@ class Supervisor:
                 if bad == 0:
                     v[var] = self.network_ids(self.args_of(answer))
                     return
-            elif sh.pattern_match(answer, v[var], self.utf8):
+            elif sh.pattern_match(answer, v[var], self.shell_utf8):
                 v["gotValidInput"] = "true"
                 return  # the default UUID list was left as it is
             else:
@@ -778,7 +786,7 @@ class Supervisor:
                     v["HOST_PACKAGE"] = self.package_id(self.args_of(answer))
                     self.echo("entered %s and got %s" % (answer, v["HOST_PACKAGE"]), lineno=440)
                     return
-            elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"]), self.utf8):
+            elif sh.pattern_match(answer, self.unq(v["HOST_PACKAGE"]), self.shell_utf8):
                 v["gotValidInput"] = "true"
                 return
             else:
@@ -989,7 +997,7 @@ class Supervisor:
         for name in sorted((set(env) | pending) - {"_"}, key=sh.to_bytes):
             if not _IDENT.fullmatch(name):
                 continue                            # never became a shell variable
-            listing.append("declare -x %s=%s\n" % (name, sh.declare_value(env[name], self.utf8)) if name in env else "declare -x %s\n" % name)
+            listing.append("declare -x %s=%s\n" % (name, sh.declare_value(env[name], self.shell_utf8)) if name in env else "declare -x %s\n" % name)
         self.write_out("".join(listing), 546)
 
     # ------------------------------------------------------------------
