@@ -441,3 +441,18 @@ def make_locales(seed: int) -> Scenario:
 @pytest.mark.parametrize("block", range(3))
 def test_property_fuzzed_locale_settings(ref_root, block):
     assert _sweep(ref_root, make_locales, range(20 * block, 20 * (block + 1))) == []
+
+
+def test_inherited_variables_that_reconfigure_bash(ref_root, tmp_path):
+    """Refused: what would put the reference's bash into another mode.  Followed: what makes no difference."""
+    (tmp_path / "rc").write_text("echo sourced\n")
+    for env in ({"POSIXLY_CORRECT": "1"}, {"POSIXLY_CORRECT": ""}, {"SHELLOPTS": "xtrace"}, {"BASHOPTS": "nullglob"}, {"BASH_ENV": str(tmp_path / "rc")},
+                {"BASH_ENV": "~/.bashenv"}):
+        sc = Scenario(name="reconf", stdin="\n" * 8 + "yes\n", env=env)
+        mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+        assert mine.exit_status == 2 and "refusing to go on" in mine.stderr and mine.calls == [] and mine.stdout == "", env
+    sc = Scenario(name="noreconf", stdin="\n\n\n\n\n*\n\n\n\nyes\n", env={"GLOBIGNORE": "*.tf:ansible", "BASH_ENV": "/nonexistent", "ENV": "/x", "BASH_COMPAT": "4.4",
+                                                                         "TMOUT": "1", "FUNCNEST": "3", "EXECIGNORE": "*/sleep"})
+    theirs = run_reference(sc, ref_root)
+    mine = run_in_sandbox(rp.REPLACEMENT_ARGV, ref_root, sc, extra_env=rp.REPLACEMENT_ENV)
+    assert theirs.diff(mine) == []

@@ -429,6 +429,18 @@ class Supervisor:
         rt = self.rt
         # a function exported by the caller (`export -f`) is defined in the script's bash before line 1, and one named
         # like a command of the script would be run in its place
+        # variables that reconfigure bash itself when it *inherits* them: the reference would run in another mode
+        # (posix mode alone changes the outcome of half of all odd inputs), which is not restated
+        for name, why in (("POSIXLY_CORRECT", "puts bash into posix mode"), ("POSIX_PEDANTIC", "puts bash into posix mode"),
+                          ("SHELLOPTS", "switches shell options on before the script starts"),
+                          ("BASHOPTS", "switches shell options on before the script starts")):
+            if name in rt.env:
+                rt.err("%s: refusing to go on: %s in the environment %s; unset it\n" % (self.program, name, why))
+                raise ScriptExit(2)
+        startup_file = rt.env.get("BASH_ENV", "")
+        if startup_file and (any(c in startup_file for c in "$`~") or os.path.exists(os.path.join(rt.root, startup_file))):
+            rt.err("%s: refusing to go on: BASH_ENV names a file bash would run before the script; unset it\n" % self.program)
+            raise ScriptExit(2)
         for key, value in rt.env.items():
             if key.startswith("BASH_FUNC_") and key.endswith("%%") and value.startswith("() {") and key[10:-2] in _COMMAND_WORDS:
                 rt.err("%s: refusing to go on: the environment exports a shell function named %s, which the script would run "
