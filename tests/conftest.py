@@ -35,6 +35,26 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: runs on the round-end B200 box (no GPU needed; see conftest)")
 
 
+@pytest.hookimpl(tryfirst=True)
+def pytest_cmdline_main(config):
+    """The suite is ~1 500 process-spawning tests: ten minutes on one core, under three on eight.  When
+    pytest-xdist is there and nobody chose a worker count (``-n``, ``-p no:xdist``, ``--pdb``), run the whole
+    directory on the cores the machine has.  ``TK8S_TEST_WORKERS=0`` keeps it in one process."""
+    workers = os.environ.get("TK8S_TEST_WORKERS", "")
+    if not config.pluginmanager.hasplugin("xdist") or getattr(config.option, "numprocesses", None) is not None \
+            or getattr(config.option, "usepdb", False) or getattr(config.option, "collectonly", False) or workers == "0" \
+            or os.environ.get("PYTEST_XDIST_WORKER"):
+        return None
+    if len(config.args) != 1 or os.path.basename(os.path.normpath(config.args[0])) != "tests":
+        return None                                   # a single file or test: not worth the workers' start-up
+    count = int(workers) if workers.isdigit() else min(8, os.cpu_count() or 1)
+    if count >= 2:
+        config.option.numprocesses = count
+        config.option.dist = "load"
+        config.option.tx = ["popen"] * count
+    return None
+
+
 #: not added to the box run: hypothesis sweeps against the live reference (minutes
 #: each), and tests whose ``*_on_box`` twin is marked in the file itself
 _NOT_ON_BOX = ("test_property_", "test_replacement_matches_golden[", "test_five_of_five", "test_hypothesis_",
