@@ -90,3 +90,65 @@ def test_sigpipe_kills_like_a_shell_script():
 
 def test_sigpipe_same_as_reference(ref_root):
     assert _reader_goes_away(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root) == _reader_goes_away(["./setup.sh"], None, ref_root)
+
+
+# --- a tool that a signal kills, with no signal sent to the script itself (the OOM killer, a crash) -----
+def _tool_dies_of(argv, env_extra, workspace_src, tool, first, signame):
+    import re
+    with Sandbox(workspace_src, CONFIGS[0]) as sbx:
+        path = os.path.join(sbx.bin, tool)
+        os.rename(path, os.path.join(sbx.bin, "stub-of-" + tool))
+        with open(path, "w") as fh:
+            fh.write('#!/bin/sh\nif [ "$1" = "%s" ]; then kill -%s $$; fi\nexit 0\n' % (first, signame))
+        os.chmod(path, 0o755)
+        p = subprocess.run(list(argv), cwd=sbx.workspace, input=CONFIGS[0].stdin.encode(), stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                           env=sbx.env(env_extra), timeout=60)
+        err = re.sub(r"line (\d+): +\d+ ", r"line \1: <PID> ", p.stderr.decode(errors="replace").replace(sbx.tmp, "<SBX>"))
+        return p.returncode, p.stdout.decode(errors="replace")[-60:], err[-300:]
+
+
+KILLED = [("terraform", "get", "KILL", 137, "./setup.sh: line 138: <PID> Killed                  terraform get\n"),
+          ("terraform", "apply", "SEGV", 139, "./setup.sh: line 138: <PID> Segmentation fault      terraform apply\n"),
+          ("terraform", "get", "TERM", 143, "Terminated\n"),
+          ("ansible-playbook", "-i", "ABRT", 134, "./setup.sh: line 111: <PID> Aborted                 ansible-playbook -i hosts clusterUp.yml\n"),
+          ("sleep", "2", "HUP", 129, "./setup.sh: line 8: <PID> Hangup                  sleep 2\n"),
+          ("terraform", "get", "INT", 130, ""), ("terraform", "get", "PIPE", 141, ""),
+          ("curl", "--connect-timeout", "INT", -signal.SIGINT, ""), ("date", "+%s", "INT", -signal.SIGINT, "")]
+
+
+@pytest.mark.parametrize("tool,first,signame,status,said", KILLED, ids=["%s-%s-%s" % k[:3] for k in KILLED])
+def test_tool_killed_by_a_signal(tool, first, signame, status, said):
+    """bash reports a foreground command that a signal killed (not SIGINT, not SIGPIPE; for SIGTERM the bare word),
+    and takes the SIGINT death of the only command of a $(...) for its own."""
+    got = _tool_dies_of(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, WORKSPACE_TEMPLATE, tool, first, signame)
+    assert got[0] == status and got[2].endswith(said) and (said != "" or "<PID>" not in got[2])
+
+
+@pytest.mark.parametrize("tool,first,signame,status,said", KILLED, ids=["%s-%s-%s" % k[:3] for k in KILLED])
+def test_tool_killed_by_a_signal_same_as_reference(ref_root, tool, first, signame, status, said):
+    assert _tool_dies_of(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root, tool, first, signame) == \
+        _tool_dies_of(["./setup.sh"], None, ref_root, tool, first, signame)
+
+
+def _quit_at_first_prompt(argv, env_extra, workspace_src):
+    with Sandbox(workspace_src, CONFIGS[0]) as sbx:
+        proc = subprocess.Popen(list(argv), cwd=sbx.workspace, stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                                env=sbx.env(env_extra), start_new_session=True)
+        log, last, since = os.path.join(sbx.state, "calls.log"), -1, time.time()
+        while time.time() - since < 0.6:                # the tools stop being called: the script sits at its first prompt
+            size = os.path.getsize(log) if os.path.exists(log) else 0
+            if size != last:
+                last, since = size, time.time()
+            time.sleep(0.02)
+        os.killpg(proc.pid, signal.SIGQUIT)             # Ctrl-\\
+        out, err = proc.communicate(timeout=30)
+        return proc.returncode, out.decode()[-20:], err.decode()
+
+
+def test_sigquit_at_a_prompt():
+    """The prompt of getArgument is read by the subshell of a $(...): SIGQUIT kills that (131, errexit), bash itself ignores it."""
+    assert _quit_at_first_prompt(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, WORKSPACE_TEMPLATE) == (131, "---------------\n", "")
+
+
+def test_sigquit_at_a_prompt_same_as_reference(ref_root):
+    assert _quit_at_first_prompt(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root) == _quit_at_first_prompt(["./setup.sh"], None, ref_root)

@@ -24,7 +24,7 @@ import signal
 import sys
 from typing import Optional, Sequence
 
-from .runtime import HostRuntime
+from .runtime import HostRuntime, SubshellQuit
 from .supervisor import Supervisor
 
 
@@ -39,8 +39,20 @@ def main(argv: Optional[Sequence[str]] = None, root: str = ".") -> int:
     except (ValueError, OSError):
         pass                                                # not the main thread: leave it
     rt = HostRuntime(root=root)
+
+    def on_sigquit(signum, frame):
+        # a non-interactive bash ignores SIGQUIT; the subshell of a $(...) does not.  A handler rather than SIG_IGN,
+        # so that the tools started from here get the default action back on exec
+        if rt.subshell_read:
+            raise SubshellQuit()
+    try:
+        signal.signal(signal.SIGQUIT, on_sigquit)
+    except (ValueError, OSError):
+        pass
     try:
         return Supervisor(rt, program=rt.env.get("TK8S_PROGRAM") or "./setup.sh").main(args)
+    except SubshellQuit:
+        return 128 + signal.SIGQUIT                         # the substitution's status, which errexit makes the script's
     except KeyboardInterrupt:
         signal.signal(signal.SIGINT, signal.SIG_DFL)
         os.kill(os.getpid(), signal.SIGINT)

@@ -77,7 +77,7 @@ class ModelRuntime(Runtime):
         return super().command_exists(name)
 
     # -- clock -------------------------------------------------------------
-    def sleep(self, seconds: int, where: str = "") -> int:
+    def sleep(self, seconds: int, where: str = "", job=None) -> int:
         return self.run(["sleep", str(seconds)], where=where)[0]
 
     def epoch(self, where: str = "") -> Tuple[int, str]:
@@ -85,7 +85,7 @@ class ModelRuntime(Runtime):
 
     # -- tools -------------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False, job=None) -> Tuple[int, str]:
         tool, args = argv[0], list(argv[1:])
         self._n_calls += 1
         if self._n_calls > self.max_calls:

@@ -36,11 +36,17 @@ class ScriptExit(Exception):
         self.status = status
 
 
+class SubshellQuit(Exception):
+    """SIGQUIT arrived while the script stood in for a ``$(...)`` subshell blocked in ``read``."""
+
+
 class Runtime:
     """Abstract boundary; see :class:`HostRuntime`."""
 
     root: str
     env: Dict[str, str]
+    #: the prompt being waited at belongs to a command substitution (setup.sh:94-111 is only ever called that way)
+    subshell_read = False
 
     # -- terminal ----------------------------------------------------------
     def out(self, text: str) -> None:
@@ -55,8 +61,11 @@ class Runtime:
 
     # -- children ----------------------------------------------------------
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
-        """Run a tool; returns (exit status, captured stdout or '').  ``where``
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False,
+            job: Optional[Tuple[str, str]] = None) -> Tuple[int, str]:
+        """Run a tool; returns (exit status, captured stdout or '').  ``job`` = (label, command text as the
+        script spells it) for a command bash runs in the foreground: when a signal other than SIGINT/SIGPIPE
+        kills it, bash reports that (``LABEL: <pid> Killed   terraform apply``).  ``where``
         ("setup.sh: line 157") prefixes the shell's own diagnostics, e.g. when
         the tool is not installed.  ``lone_subst``: the tool is the only command
         of a ``$(...)`` (``$(triton env)``, ``$(curl ...)``, `` `date +%s` ``):
@@ -64,7 +73,7 @@ class Runtime:
         shell level it had added back out of SHLVL first -- see :func:`child_env`."""
         raise NotImplementedError
 
-    def sleep(self, seconds: int, where: str = "") -> int:
+    def sleep(self, seconds: int, where: str = "", job: Optional[Tuple[str, str]] = None) -> int:
         """``sleep N``; returns its exit status."""
         raise NotImplementedError
 
@@ -209,7 +218,8 @@ class HostRuntime(Runtime):
         return bashsem.read_builtin(self._next_byte)
 
     def run(self, argv: Sequence[str], cwd: str = ".", stdout: str = INHERIT,
-            stderr: str = INHERIT, where: str = "", lone_subst: bool = False) -> Tuple[int, str]:
+            stderr: str = INHERIT, where: str = "", lone_subst: bool = False,
+            job: Optional[Tuple[str, str]] = None) -> Tuple[int, str]:
         # A child inherits our descriptors as they are -- closed ones included (`./setup.sh 2>&-`);
         # naming 0/1/2 explicitly would make Popen dup them and fail on a closed one.
         def inherit(fd: int, std: int):
@@ -258,16 +268,25 @@ class HostRuntime(Runtime):
                 signal.signal(signal.SIGINT, restore)
         if interrupted and proc.returncode == -signal.SIGINT:
             raise KeyboardInterrupt         # the child died of it: so does the script
+        if lone_subst and proc.returncode == -signal.SIGINT:
+            raise KeyboardInterrupt         # the only command of a $(...) died of SIGINT: bash takes that for its own
         status = proc.returncode
         if status < 0:
             status = 128 - status
+            killer = -proc.returncode
+            if job is not None and killer not in (signal.SIGINT, signal.SIGPIPE):
+                # bash's notice about a foreground command that a signal killed
+                if killer == signal.SIGTERM:
+                    self.err("Terminated\n")
+                else:
+                    self.err("%s: %5d %-24s%s\n" % (job[0], proc.pid, signal.strsignal(killer) or "Unknown signal %d" % killer, job[1]))
         return status, (bashsem.from_bytes(data) if data is not None else "")
 
-    def sleep(self, seconds: int, where: str = "") -> int:
+    def sleep(self, seconds: int, where: str = "", job: Optional[Tuple[str, str]] = None) -> int:
         if self.inprocess_clock:
             time.sleep(seconds)
             return 0
-        return self.run(["sleep", str(seconds)], where=where)[0]
+        return self.run(["sleep", str(seconds)], where=where, job=job)[0]
 
     def epoch(self, where: str = "") -> Tuple[int, str]:
         if self.inprocess_clock:

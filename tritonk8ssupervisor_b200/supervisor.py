@@ -493,7 +493,7 @@ class Supervisor:
         self.echo(RULE, lineno=line - 3)
         self.echo("### " + text, lineno=line - 2)
         self.echo(RULE, lineno=line - 1)
-        self.must(self.rt.sleep(2, self.at(line)))
+        self.must(self.rt.sleep(2, self.at(line), job=(self.at(8), "sleep 2")))
 
     # ------------------------------------------------------------------
     # a1  setVarDefaults  (setup.sh:240-254)
@@ -595,7 +595,13 @@ class Supervisor:
         """``$(getArgument "message" "default")``: empty answer (or EOF) = default.
         Both branches ``echo`` unquoted.  ``lineno`` is the reference line of the
         call, which bash names when it drops a NUL byte from the substitution."""
-        answer, _ok = self.rt.read("%s (%s) " % (message, default))
+        # getArgument runs inside $(...): the process waiting at this prompt is a subshell, and a SIGQUIT from the
+        # terminal kills *it* (status 131, which errexit makes the script's) while the script's own bash ignores it
+        self.rt.subshell_read = True
+        try:
+            answer, _ok = self.rt.read("%s (%s) " % (message, default))
+        finally:
+            self.rt.subshell_read = False
         printed = sh.echo_unquoted(default if answer == "" else answer, self.root)
         if "\x00" in printed:
             self.rt.err("%s: line %d: warning: command substitution: ignored null byte in input\n" % (self.program, lineno))
@@ -1041,8 +1047,8 @@ class Supervisor:
             self.arith_eval("i++", 148, "((")
         self.cd("terraform")
         self.echo("Starting terraform tasks", lineno=155)
-        self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156))[0])
-        self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157))[0])
+        self.must(rt.run(["terraform", "get"], cwd="terraform", where=self.at(156), job=(self.at(138), "terraform get"))[0])
+        self.must(rt.run(["terraform", "apply"], cwd="terraform", where=self.at(157), job=(self.at(138), "terraform apply"))[0])
         self.echo("    terraform tasks completed", lineno=158)
         self.cd("..")
 
@@ -1207,7 +1213,8 @@ class Supervisor:
             self.rt.err("%s: line 112: cd: ansible: No such file or directory\n" % self.program)
             raise ScriptExit(1)
         self.cd("ansible")
-        self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible", where=self.at(113))[0])
+        self.must(self.rt.run(["ansible-playbook", "-i", "hosts", "clusterUp.yml"], cwd="ansible", where=self.at(113),
+                                   job=(self.at(111), "ansible-playbook -i hosts clusterUp.yml"))[0])
         self.cd("..")
 
     # ------------------------------------------------------------------
@@ -1241,7 +1248,7 @@ class Supervisor:
         up = False
         while not up:
             self.write_out(".", 62)
-            self.must(rt.sleep(1, self.at(63)))
+            self.must(rt.sleep(1, self.at(63), job=(self.at(8), "sleep 1")))
             # if ! ((`date +%s` % 15)): the clock reading is spliced into an arithmetic
             # expression.  Zero -- or an expression bash cannot evaluate -- means "poll now".
             date_status, now = rt.epoch(self.at(64))
