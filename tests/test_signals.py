@@ -152,3 +152,28 @@ def test_sigquit_at_a_prompt():
 
 def test_sigquit_at_a_prompt_same_as_reference(ref_root):
     assert _quit_at_first_prompt(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root) == _quit_at_first_prompt(["./setup.sh"], None, ref_root)
+
+
+def test_tool_killed_by_a_signal_while_cleaning(ref_root):
+    """`terraform destroy ... || true` and `ssh-keygen -R` in cleanRunner: same notice, labelled with the line of
+    the `case` / `for` they stand in."""
+    import re
+    from tritonk8ssupervisor_b200.conformance.scenario import Scenario
+    sc = Scenario(name="c", args=["-c"], stdin="yes\n", known_hosts="x\n",
+                  pre_files={"terraform/rancher.tf": "x\n", "terraform/masters.ip": "10.0.0.1\n", "terraform/hosts.ip": "10.0.1.1\n"})
+
+    def run(argv, env_extra, tool, first, signame):
+        with Sandbox(ref_root, sc) as sbx:
+            path = os.path.join(sbx.bin, tool)
+            os.remove(path)
+            with open(path, "w") as fh:
+                fh.write('#!/bin/sh\nif [ "$1" = "%s" ]; then kill -%s $$; fi\nexit 0\n' % (first, signame))
+            os.chmod(path, 0o755)
+            p = subprocess.run(list(argv) + ["-c"], cwd=sbx.workspace, input=b"yes\n", stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                               env=sbx.env(env_extra), timeout=60)
+            return p.returncode, p.stdout.decode()[-40:], re.sub(r"line (\d+): +\d+ ", r"line \1: <PID> ", p.stderr.decode())
+    for tool, first, signame in (("terraform", "destroy", "KILL"), ("terraform", "destroy", "TERM"), ("ssh-keygen", "-R", "SEGV"), ("ssh-keygen", "-R", "INT")):
+        mine = run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, tool, first, signame)
+        assert mine == run(["./setup.sh"], None, tool, first, signame)
+        if signame in ("KILL", "SEGV"):
+            assert "<PID>" in mine[2]

@@ -1319,7 +1319,8 @@ class Supervisor:
         if rt.exists("terraform/rancher.tf"):
             self.cd("terraform")
             self.echo("    destroying images...", lineno=500)
-            rt.run(["terraform", "destroy", "-force"], cwd="terraform", stderr=DEVNULL)  # `|| true`
+            rt.run(["terraform", "destroy", "-force"], cwd="terraform", stderr=DEVNULL,
+                   job=(self.at(496), "terraform destroy -force 2> /dev/null"))  # `|| true`
             self.cd("..")
         if (rt.exists("terraform/hosts.ip") and rt.exists("terraform/masters.ip")
                 and os.path.exists(self.tilde("~/.ssh/known_hosts"))):
@@ -1333,7 +1334,8 @@ class Supervisor:
             for host_key in self.args_of(recorded):
                 self.v["host_key"] = host_key
                 # `2>&1 >> /dev/null`: stderr joins the script's stdout, stdout is dropped
-                status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT, where=self.at(506))
+                status, _ = rt.run(["ssh-keygen", "-R"] + self.args_of(host_key), stdout=DEVNULL, stderr=TO_STDOUT, where=self.at(506),
+                                    job=(self.at(505), "ssh-keygen -R $host_key 2>&1 >> /dev/null"))
                 self.must(status)
         for rel in ("terraform/hosts.ip", "terraform/masters.ip", "terraform/rancher.tf"):
             _rm_rf(rt.path(rel))
