@@ -1,6 +1,7 @@
 """Standard descriptors that are closed or cannot be written: the program must
 behave like the bash script, not die with a traceback.  Expected values are
 what the reference does (compared live where a reference tree is available)."""
+import os
 import subprocess
 
 import pytest
@@ -42,3 +43,32 @@ def test_odd_descriptors(label):
 def test_odd_descriptors_same_as_reference(ref_root, label):
     redirection = CASES[label][0]
     assert _run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV, ref_root, redirection) == _run(["./setup.sh"], None, ref_root, redirection)
+
+
+@pytest.mark.parametrize("kind", ["file", "append", "offset", "devnull"])
+def test_answers_from_a_regular_file(ref_root, kind):
+    """`./setup.sh < answers.txt`: same run, and the descriptor is left at the same offset (tools that read the
+    stdin they inherit find the file where bash would have left it for them)."""
+    import subprocess
+    from tritonk8ssupervisor_b200.conformance import replay as rp
+    from tritonk8ssupervisor_b200.conformance.sandbox import Sandbox
+    from tritonk8ssupervisor_b200.conformance.scenario import Scenario
+    sc = Scenario(name="filestdin", stdin="x" * 300 + "\n\\\ncontinued\n" + "\n" * 6 + "yes\nA\nB\n" + "y" * 5000 + "\n",
+                  stdin_eaters={"terraform-apply": 1, "sleep-2": 1})
+
+    def run(argv, env_extra):
+        with Sandbox(ref_root, sc) as sbx:
+            path = os.path.join(sbx.tmp, "answers.txt")
+            with open(path, "wb") as fh:
+                fh.write(sc.stdin.encode())
+            fh = open("/dev/null", "rb") if kind == "devnull" else open(path, "ab+" if kind == "append" else "rb")
+            if kind == "offset":
+                fh.seek(1)
+            before = sbx.snapshot()
+            p = subprocess.run(list(argv), cwd=sbx.workspace, stdin=fh, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=sbx.env(env_extra), timeout=60)
+            where = os.lseek(fh.fileno(), 0, os.SEEK_CUR)
+            fh.close()
+            return sbx.observe(before, p.returncode, p.stdout, p.stderr), where
+    theirs, their_offset = run(["./setup.sh"], None)
+    mine, my_offset = run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV)
+    assert theirs.diff(mine) == [] and their_offset == my_offset
