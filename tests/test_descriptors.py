@@ -72,3 +72,34 @@ def test_answers_from_a_regular_file(ref_root, kind):
     theirs, their_offset = run(["./setup.sh"], None)
     mine, my_offset = run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV)
     assert theirs.diff(mine) == [] and their_offset == my_offset
+
+
+def _scenarios_that_say_something_on_stderr():
+    import json
+    from tritonk8ssupervisor_b200.conformance.catalog import ALL
+    names = []
+    for sc in ALL:
+        path = os.path.join(rp.golden_dir(), sc.name + ".json")
+        if os.path.exists(path) and not sc.name.endswith("__bash_setup_sh") and sc.name != "cfg_line_is_export_p":
+            with open(path, encoding="utf-8") as fh:
+                if json.load(fh)["expected"]["stderr"]:
+                    names.append(sc.name)
+    return names
+
+
+@pytest.mark.parametrize("name", _scenarios_that_say_something_on_stderr())
+def test_stdout_and_stderr_on_one_pipe(ref_root, name):
+    """`./setup.sh 2>&1 | tee log`: the diagnostics fall between the same lines of output as the reference's
+    (each `$(...)` is evaluated when the line that holds it is reached, not before)."""
+    from tritonk8ssupervisor_b200.conformance.catalog import BY_NAME
+    sc = BY_NAME[name]
+    why = rp.not_reproducible_here({"scenario": sc.to_json(), "expected": {"stderr": "ls: cannot access"}}) if "HOME" not in sc.unset_env else "home"
+    if why:
+        pytest.skip(why)
+
+    def run(argv, env_extra):
+        with Sandbox(ref_root, sc) as sbx:
+            p = subprocess.run(list(argv) + list(sc.args), cwd=sbx.workspace, input=sc.stdin.encode("utf-8", "surrogateescape"),
+                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, env=sbx.env(env_extra), timeout=60)
+            return p.returncode, p.stdout.replace(sbx.tmp.encode(), b"<SBX>")
+    assert run(rp.REPLACEMENT_ARGV, rp.REPLACEMENT_ENV) == run(sc.reference_argv(), None)

@@ -468,12 +468,13 @@ class Supervisor:
         self.banner("Running ansible tasks...", 46)
         self.run_ansible()
 
-        master = self.cat_subst("terraform/masters.ip", 53)
-        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id", 53)
         self.echo("", lineno=49)
         self.echo("Congratulations, your Kubernetes cluster setup has been complete.", lineno=50)
         self.echo("", lineno=51)
         self.echo("It will take a few minutes for all the Kubernetes process to start up before you can access Kubernetes Dashboard", lineno=52)
+        # the two `cat`s are part of the next line's argument: what they say on stderr comes after the lines above
+        master = self.cat_subst("terraform/masters.ip", 53)
+        env_id = self.cat_subst("ansible/tmp/kubernetes_environment.id", 53)
         self.echo("----> To check what processes/containers are coming up, go to http://%s:8080/env/%s/infra/containers" % (master, env_id), lineno=53)
         self.echo("    once all these containers are up, you should be able to access Kubernetes by its dashboard or using CLI", lineno=54)
         self.echo("Waiting on Kubernetes dashboard to come up.", lineno=56)
