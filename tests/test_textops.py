@@ -105,3 +105,24 @@ def test_wc_w_classifies_characters_as_the_locale_does():
         for env, utf8 in (({"LC_ALL": "C"}, False), ({"LANG": "C.UTF-8"}, True)):
             real = int(subprocess.run(["wc", "-w"], input=to_bytes(text), capture_output=True, env=dict(env, PATH="/usr/bin:/bin")).stdout)
             assert tx.wc_w(text, utf8=utf8) == real, (ascii(text), utf8)
+
+
+def test_grep_on_input_with_nul_bytes_matches_the_real_grep():
+    """Binary input: nothing is printed, `binary file matches` is said if a line was selected -- and while it
+    looks for matches grep lets a NUL end a line, so `^NAME.*ID$` does not match `NAME \\0 ID`."""
+    import random
+    import subprocess
+    from tritonk8ssupervisor_b200 import textops as tx
+    r = random.Random(4)
+    pieces = ["NAME", "ID", " ", "  ", "\0", "\n", "x-kvm-1", "kubernetes", "Service Unavailable", "k8s_POD.a_dashboard", "a", "SHA256", ""]
+    patterns = [("^NAME.*ID$", r"^NAME.*ID$", True, False), ("^NAME *ID$", r"^NAME *ID$", True, False), ("\\-kvm-", r"-kvm-", False, False),
+                ("kubernetes", r"kubernetes", False, True), ("k8s_POD.*dashboard", r"k8s_POD.*dashboard", False, False), ("^$", r"^$", True, False),
+                ("^SHA256", r"^SHA256", False, False)]
+    for _ in range(300):
+        text = "".join(r.choice(pieces) for _ in range(r.randint(1, 8))) + r.choice(["\n", "", "\0"])
+        bre, py, invert, icase = r.choice(patterns)
+        argv = ["grep"] + (["-v"] if invert else []) + (["-i"] if icase else []) + [bre]
+        real = subprocess.run(argv, input=text.encode(), capture_output=True, env={"LC_ALL": "C", "PATH": "/usr/bin:/bin"})
+        said = []
+        mine = tx.grep(text, py, invert=invert, ignore_case=icase, binary=lambda: said.append(1))
+        assert (mine.encode(), bool(said)) == (real.stdout, b"binary file matches" in real.stderr), (text, bre)

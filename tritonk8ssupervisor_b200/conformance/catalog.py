@@ -134,6 +134,9 @@ EDGE: List[Scenario] = [
              note="... 'i': the loop counter of setup.sh:148 has the export attribute from then on, terraform sees i=2"),
     Scenario(name="cfg_line_assigns_a_readonly_variable", stdin=_answers("", "-e a\\\\nUID=0\\\\nQ=", "", "", "", "", "", "", "", "yes"),
              note="... 'UID=0': `./setup.sh: line 546: UID: readonly variable`, status 1, errexit; config.tmp stays behind"),
+    Scenario(name="net_header_line_holds_a_nul", stdin=BLANK8 + YES, networks="NAME \x00 ID\n" + triton_table(DOC_NETWORKS).split("\n", 1)[1],
+             note="binary input: while it looks for matches grep lets a NUL end a line, so `^NAME.*ID$` does not match the "
+                  "header `NAME \\0 ID`, `grep -v` selects it and says `binary file matches` (setup.sh:257)"),
     Scenario(name="net_no_public_network", networks=triton_table(DOC_NETWORKS[:1] + DOC_NETWORKS[2:]),
              stdin=BLANK8 + YES, note="no Joyent-SDC-Public row: default position 1 (setup.sh:311)"),
     Scenario(name="net_single_row_table", networks=triton_table(DOC_NETWORKS[1:2]), stdin=_answers("", "", "", "", "", "2", "1", "", "", "yes"),

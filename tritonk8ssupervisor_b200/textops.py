@@ -34,7 +34,7 @@ def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = Fals
     """``grep [-v] [-i] PATTERN`` with a Python-syntax equivalent of the BRE.
 
     What grep takes for binary data it does not print.  Input holding a NUL byte is binary as a
-    whole: no line comes out.  When the locale's character set is UTF-8 (``utf8``), a selected line
+    whole: no line comes out (and while matching, each NUL ends a line).  When the locale's character set is UTF-8 (``utf8``), a selected line
     that is not valid UTF-8 is left out, the others are printed.  Either way grep says ``binary
     file matches`` on stderr, once, if it held anything back -- ``binary()`` is called then."""
     rx = re.compile(pattern, re.I if ignore_case else 0)
@@ -44,13 +44,16 @@ def grep(text: str, pattern: str, invert: bool = False, ignore_case: bool = Fals
             # a byte that is no character is matched by nothing, not even by `.`; Python's `.` stops at a newline
             line = "".join("\n" if "\udc80" <= c <= "\udcff" else c for c in line)
         return rx.search(line) is not None
-    selected = [l for l in lines(text) if hit(l) != invert]
     held_back = False
     if "\0" in text:
-        held_back, selected = bool(selected), []
-    elif utf8:
-        clean = [l for l in selected if not any("\udc80" <= c <= "\udcff" for c in l)]
-        held_back, selected = len(clean) != len(selected), clean
+        # binary input: a NUL ends a line just as a newline does while grep looks for matches (so `.` never
+        # gets to match one), and nothing is printed
+        held_back, selected = any(hit(l) != invert for l in lines(text.replace("\0", "\n"))), []
+    else:
+        selected = [l for l in lines(text) if hit(l) != invert]
+        if utf8:
+            clean = [l for l in selected if not any("\udc80" <= c <= "\udcff" for c in l)]
+            held_back, selected = len(clean) != len(selected), clean
     if held_back and binary is not None:
         binary()
     return unlines(selected)
